@@ -1,0 +1,158 @@
+/* slq.h -- C ABI of libslq, a B200 (sm_100a) stochastic-Lanczos-quadrature engine.
+ *
+ * This is the drop-in boundary for ONE hot path of peekxc/primate (citations are relative to the reference
+ * checkout): probe generation -> probe-blocked Lanczos -> Golub-Welsch quadrature -> f(theta).tau -> running
+ * mean/variance.  It replaces the pybind11 module `primate._lanczos` (src/primate/_lanczos.cpp:86-112) and
+ * the per-probe Python loop wrapped around it (src/primate/operators.py:126-151, src/primate/trace.py:107-116).
+ *
+ * Conventions
+ *  - Plain pointers and sizes only.  Every `*_dev` pointer is CUDA device memory owned by the CALLER (the
+ *    Python host side allocates it as torch tensors); the library never allocates on the hot path.
+ *  - A "probe block" is a dense n x k panel stored ROW-MAJOR (probe-minor): element (row r, probe p) lives at
+ *    X[r*k + p], so the k values of one row are one contiguous, 16-byte-aligned vector.  k must be a power of
+ *    two in [1, 64].  (The reference stores probes F-ordered (N,k), src/primate/random.py:74-78.)
+ *  - `stream` is a cudaStream_t passed as void*; all work is enqueued on it and is stream-ordered.  No entry
+ *    point synchronises the device unless documented.
+ *  - Every function returns SLQ_OK (0) or a negative error code; slq_last_error() returns a thread-local
+ *    message.  There is NO CPU fallback: without a CUDA device every compute entry fails with SLQ_ERR_CUDA.
+ */
+#ifndef SLQ_H_
+#define SLQ_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+#if defined(__GNUC__)
+#pragma GCC visibility push(default) /* the entry points below are the only exported symbols of libslq.so */
+#endif
+
+#define SLQ_OK 0
+#define SLQ_ERR_ARG (-1)         /* invalid argument (reference: TypeError / ValueError / assert)           */
+#define SLQ_ERR_CUDA (-2)        /* CUDA runtime error or no device                                         */
+#define SLQ_ERR_UNSUPPORTED (-3) /* valid request the library does not implement                            */
+#define SLQ_ERR_CALLBACK (-4)    /* a user operator callback returned non-zero (reference: Python exception) */
+
+enum slq_dtype { SLQ_F32 = 0, SLQ_F64 = 1 };
+
+/* Built-in spectral functions; mirror of primate.special._BUILTIN_MATRIX_FUNCTIONS and param_callable
+ * (src/primate/special.py:7,78-107).  params[] meaning: EXP: t; SMOOTHSTEP: a, b; NUMRANK: threshold;
+ * SOFTSIGN: q (integer valued). */
+enum slq_fun {
+  SLQ_FUN_IDENTITY = 0,
+  SLQ_FUN_ABS = 1,
+  SLQ_FUN_SQRT = 2,
+  SLQ_FUN_LOG = 3, /* log(max(x, DBL_EPSILON)), special.py:90 */
+  SLQ_FUN_INV = 4,
+  SLQ_FUN_EXP = 5,
+  SLQ_FUN_SMOOTHSTEP = 6,
+  SLQ_FUN_NUMRANK = 7,
+  SLQ_FUN_SOFTSIGN = 8,
+  SLQ_FUN_NONE = -1 /* do not evaluate f: only theta/tau are produced */
+};
+
+typedef struct slq_op slq_op; /* opaque symmetric linear operator, device resident */
+typedef void* slq_stream;     /* cudaStream_t */
+
+/* User operator: Y[n x k] = A * X[n x k] on device panels in the block layout above, enqueued on `stream`
+ * (or completed before returning).  Replaces the C++20 `LinearOperator`/`SupportsMatrixMult` concepts
+ * (src/primate/include/linear_operator.h:25-29,59-62) and PyLinearOperator (include/pylinop.h:17-40). */
+typedef int (*slq_matmat_fn)(void* ctx, const void* X_dev, void* Y_dev, int64_t n, int k, int dtype,
+                             slq_stream stream);
+
+/* ---- library ------------------------------------------------------------------------------------------ */
+int slq_version(void);
+const char* slq_last_error(void);
+/* SM count and compute capability of the current device (fails with SLQ_ERR_CUDA without one). */
+int slq_device_info(int* sm_count, int* cc_major, int* cc_minor);
+
+/* ---- operators (replace the per-call matrix wrappers: include/eigen_operators.h:18-104, _lanczos.cpp:93) - */
+/* CSR with int32 indices; arrays stay owned by the caller and must outlive the handle.  A must be symmetric
+ * (as in the reference, which feeds the same symmetric matrix in CSC form). Column indices sorted per row is
+ * recommended (keeps the summation order of Eigen's column sweep) but not required. */
+int slq_csr_create(int64_t n, int64_t nnz, const int32_t* rowptr_dev, const int32_t* colidx_dev,
+                   const void* vals_dev, int dtype, slq_op** out);
+/* Dense symmetric n x n, leading dimension ld (row- or column-major is the same for a symmetric matrix). */
+int slq_dense_create(int64_t n, const void* A_dev, int64_t ld, int dtype, slq_op** out);
+/* Matrix-free operator driven by a callback (device panels in, device panels out). */
+int slq_callback_create(int64_t n, int dtype, slq_matmat_fn fn, void* ctx, slq_op** out);
+int slq_op_destroy(slq_op* op);
+int64_t slq_op_rows(const slq_op* op);
+int slq_op_dtype(const slq_op* op);
+int64_t slq_op_nnz(const slq_op* op);
+/* Y = A X for a probe block (the SpMM on its own; eigen_operators.h:66-99 `matvec`/`matmat`). */
+int slq_op_matmat(slq_op* op, const void* X_dev, void* Y_dev, int k, slq_stream stream);
+
+/* ---- probes (src/primate/random.py:22-29,47-80 on NumPy's PCG64) ---------------------------------------- */
+/* Rademacher block: X[r*k + p] = +1 if the MSB of PCG64 raw output #((first_probe+p)*n + r) is set else -1,
+ * for the generator whose 128-bit (state, inc) BEFORE any draw are given as {hi, lo} pairs.  Bit-exact with
+ * primate.random.isotropic(pdf="rademacher") drawn column by column from that generator. */
+int slq_probes_rademacher(const uint64_t state_hi_lo[2], const uint64_t inc_hi_lo[2], uint64_t first_probe,
+                          int k, int64_t n, int dtype, void* X_dev, slq_stream stream);
+/* Raw PCG64 outputs #offset.. (testing aid for the generator itself). */
+int slq_pcg64_raw(const uint64_t state_hi_lo[2], const uint64_t inc_hi_lo[2], uint64_t offset, int64_t count,
+                  uint64_t* out_dev, slq_stream stream);
+/* Layout helpers between the reference's F-ordered (n,k) panels (k contiguous columns) and probe blocks. */
+int slq_block_from_columns(const void* cols_dev, int64_t n, int k, int dtype, void* X_dev, slq_stream stream);
+int slq_block_to_columns(const void* X_dev, int64_t n, int k, int dtype, void* cols_dev, slq_stream stream);
+
+/* ---- Lanczos (src/primate/include/lanczos.h:92-149 + orth_vector :43-66, blocked over k probes) --------- */
+/* Bytes of caller-provided scratch needed by slq_lanczos. */
+size_t slq_lanczos_workspace_bytes(int64_t n, int k, int ncv, int dtype);
+/* Runs `deg` steps of Paige-A27 Lanczos independently for each of the k columns of X.
+ *   X_dev      n x k probe block, start vectors; CLOBBERED (the reference clobbers `v`, lanczos.h:114,127).
+ *   rtol       early-break threshold is sqrt(n)*rtol per probe (lanczos.h:110,140).
+ *   orth       number of stored Lanczos vectors re-projected per step, walking back cyclically from the
+ *              current one (lanczos.h:133-136); fresh-basis semantics (all ncv columns start at zero).
+ *   ncv        number of Lanczos vectors kept (>= 2); the reference's Q.shape[1] (_lanczos.cpp:94).
+ *   alpha_dev  k x (deg+1), probe-major; alpha[p][j], j < deg.  Written from zero (tails stay 0 after a break).
+ *   beta_dev   k x (deg+1); beta[p][0] = 0, beta[p][j+1] = ||v_j||.
+ *   steps_dev  k int32: number of steps executed per probe (deg unless the early break fired).  May be NULL.
+ *   xnorm2_dev k doubles: ||x_p||^2 of the start vectors (operators.py:147).  May be NULL.
+ *   Q_dev      NULL, or n x ncv x k: the normalised Lanczos vectors, Q[(c*n + r)*k + p] (for k == 1 this is
+ *              exactly the reference's F-ordered (n, ncv) basis, lanczos.py:103).
+ */
+int slq_lanczos(slq_op* op, void* X_dev, int k, int deg, double rtol, int orth, int ncv, void* alpha_dev,
+                void* beta_dev, int32_t* steps_dev, double* xnorm2_dev, void* Q_dev, void* workspace_dev,
+                size_t workspace_bytes, slq_stream stream);
+
+/* ---- quadrature (src/primate/integrate.py:58-64, tridiag.py:7-43, tqli.py:15-90) ------------------------ */
+/* For each of k Jacobi matrices T_p = tridiag(alpha[p][0:deg], beta[p][1:deg]) (row stride ld, dtype as the
+ * Lanczos run): Ritz values theta (ascending) and Golub-Welsch weights tau = (first eigenvector row)^2 by an
+ * implicit-shift QL sweep, one warp per matrix; then y[p] = scale[p] * sum_i f(theta_i) tau_i fused in the
+ * same kernel (operators.py:150).  Any of theta_dev/tau_dev (k x deg doubles), y_dev (k doubles),
+ * scale_dev (k doubles; NULL = 1) and info_dev (k int32; #eigenvalues that hit the iteration cap) may be NULL.
+ * fun = SLQ_FUN_NONE skips f.  params: 4 doubles (host). */
+int slq_quadrature(const void* alpha_dev, const void* beta_dev, int dtype, int k, int deg, int ld, int fun,
+                   const double* params, const double* scale_dev, double* theta_dev, double* tau_dev,
+                   double* y_dev, int32_t* info_dev, slq_stream stream);
+/* As slq_quadrature but also returns c_p = Y f(Theta) Y^T e_1 (k x deg doubles), the Krylov coefficients of
+ * f(A)x (operators.py:122-124).  Needs deg*deg*k doubles of scratch. */
+int slq_funm_coeffs(const void* alpha_dev, const void* beta_dev, int dtype, int k, int deg, int ld, int fun,
+                    const double* params, double* coeffs_dev, double* theta_dev, double* tau_dev,
+                    double* scratch_dev, int32_t* info_dev, slq_stream stream);
+/* y[p] = scale[p] * sum_i f(theta[p][i]) * tau[p][i]   (fused evaluation on caller-provided nodes). */
+int slq_apply_fun(const double* theta_dev, const double* tau_dev, int k, int deg, int fun, const double* params,
+                  const double* scale_dev, double* y_dev, slq_stream stream);
+/* FTTR weights (src/primate/fttr.py:5-29) for caller-provided nodes: theta k x deg -> tau k x deg. */
+int slq_fttr(const double* theta_dev, const void* alpha_dev, const void* beta_dev, int dtype, int k, int deg,
+             int ld, double* tau_dev, slq_stream stream);
+
+/* ---- running statistics (src/primate/stats.py:66-86, estimators.py:128-141) ----------------------------- */
+/* Chan/Welford merge of a batch of m samples into state_dev = {count, mean, M2} (3 doubles, device). */
+int slq_stats_update(const double* y_dev, int m, double* state_dev, slq_stream stream);
+
+/* ---- f(A) X on the same engine (src/primate/operators.py:102-124) --------------------------------------- */
+/* Y[n x k] = sum_j Q_j * (coeffs[p][j] * xnorm[p])  with Q as produced by slq_lanczos (n x ncv x k, ncv>=deg). */
+int slq_basis_combine(const void* Q_dev, int64_t n, int k, int deg, int dtype, const double* coeffs_dev,
+                      const double* xnorm2_dev, void* Y_dev, slq_stream stream);
+
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
+#ifdef __cplusplus
+}
+#endif
+#endif /* SLQ_H_ */

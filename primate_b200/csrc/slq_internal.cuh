@@ -1,0 +1,178 @@
+// Internal helpers shared by the libslq translation units (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <cstdarg>
+#include <cstdio>
+
+#include "slq.h"
+
+#if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
+#error "libslq is written for sm_100a (B200) only"
+#endif
+
+namespace slq {
+
+// ---- error reporting -------------------------------------------------------------------------------------
+char* err_buf();  // thread-local, 512 bytes
+int fail(int code, const char* fmt, ...);
+
+#define SLQ_CUDA(expr)                                                                                 \
+  do {                                                                                                 \
+    cudaError_t _e = (expr);                                                                           \
+    if (_e != cudaSuccess)                                                                             \
+      return ::slq::fail(SLQ_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+  } while (0)
+
+#define SLQ_LAUNCH_CHECK()                                                                             \
+  do {                                                                                                 \
+    cudaError_t _e = cudaGetLastError();                                                               \
+    if (_e != cudaSuccess)                                                                             \
+      return ::slq::fail(SLQ_ERR_CUDA, "kernel launch failed: %s (%s:%d)", cudaGetErrorString(_e), __FILE__, __LINE__); \
+  } while (0)
+
+#define SLQ_REQUIRE(cond, ...) \
+  do {                         \
+    if (!(cond)) return ::slq::fail(SLQ_ERR_ARG, __VA_ARGS__); \
+  } while (0)
+
+int sm_count();  // cached; <= 0 if no device
+
+inline bool is_pow2(int k) { return k > 0 && (k & (k - 1)) == 0; }
+inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+inline size_t dtype_size(int dtype) { return dtype == SLQ_F64 ? 8 : 4; }
+
+// ---- operator handle -------------------------------------------------------------------------------------
+enum OpKind { OP_CSR = 0, OP_DENSE = 1, OP_CALLBACK = 2 };
+
+}  // namespace slq
+
+struct slq_op {
+  int kind;
+  int dtype;
+  int64_t n;
+  int64_t nnz;
+  // CSR
+  const int32_t* rowptr;
+  const int32_t* colidx;
+  const void* vals;
+  // dense
+  const void* dense;
+  int64_t ld;
+  // callback
+  slq_matmat_fn fn;
+  void* ctx;
+};
+
+namespace slq {
+
+// ---- vector packs: V scalars moved with one 4/8/16-byte access -------------------------------------------
+template <typename T, int V>
+struct alignas(sizeof(T) * V) Pack {
+  T v[V];
+};
+
+enum CachePolicy { LD_DEFAULT = 0, LD_STREAM = 1, LD_READONLY = 2 };
+
+template <int BYTES>
+struct RawBytes;
+template <>
+struct RawBytes<4> {
+  using type = unsigned int;
+};
+template <>
+struct RawBytes<8> {
+  using type = uint2;
+};
+template <>
+struct RawBytes<16> {
+  using type = uint4;
+};
+
+// Vector load of V scalars with a cache policy: LD_STREAM = evict-first (read once), LD_READONLY = non-coherent
+// path (re-used panels: the gathered probe rows), LD_DEFAULT = plain.
+template <typename T, int V, int POLICY>
+__device__ __forceinline__ Pack<T, V> ld_pack(const T* p) {
+  using R = typename RawBytes<sizeof(T) * V>::type;
+  R raw;
+  if (POLICY == LD_STREAM)
+    raw = __ldcs(reinterpret_cast<const R*>(p));
+  else if (POLICY == LD_READONLY)
+    raw = __ldg(reinterpret_cast<const R*>(p));
+  else
+    raw = *reinterpret_cast<const R*>(p);
+  Pack<T, V> out;
+  *reinterpret_cast<R*>(&out) = raw;
+  return out;
+}
+
+template <typename T, int V, bool STREAM>
+__device__ __forceinline__ void st_pack(T* p, const Pack<T, V>& x) {
+  using R = typename RawBytes<sizeof(T) * V>::type;
+  R raw = *reinterpret_cast<const R*>(&x);
+  if (STREAM)
+    __stcs(reinterpret_cast<R*>(p), raw);
+  else
+    *reinterpret_cast<R*>(p) = raw;
+}
+
+// Probe-block thread mapping for scalar type T and block width K: each thread owns V adjacent probes of a row;
+// LPR threads cover one row.
+template <typename T, int K>
+struct BlockMap {
+  static constexpr int VMAX = 16 / (int)sizeof(T);
+  static constexpr int V = K < VMAX ? K : VMAX;
+  static constexpr int LPR = K / V;  // threads per row (<= 32 for K <= 64 fp64 / 128 fp32)
+  static_assert(LPR <= 32, "block width too large");
+};
+
+constexpr int NT = 256;  // threads per CTA for all streaming kernels
+constexpr int NWARP = NT / 32;
+
+// Deterministic per-CTA reduction of per-thread accumulators that belong to probe slots (tid % LPR)*V + i.
+// Result: for NACC accumulators, part[a*K + probe] written to `out` (one row of the per-CTA partial table).
+template <int K, int V, int LPR, int NACC>
+__device__ __forceinline__ void cta_reduce_slots(double (&acc)[NACC][V], double* out, double* smem /* NWARP*NACC*K */) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int a = 0; a < NACC; ++a)
+#pragma unroll
+    for (int i = 0; i < V; ++i) {
+      double x = acc[a][i];
+#pragma unroll
+      for (int off = 16; off >= LPR; off >>= 1) x += __shfl_xor_sync(0xffffffffu, x, off);
+      acc[a][i] = x;
+    }
+  if (lane < LPR) {
+#pragma unroll
+    for (int a = 0; a < NACC; ++a)
+#pragma unroll
+      for (int i = 0; i < V; ++i) smem[(warp * NACC + a) * K + lane * V + i] = acc[a][i];
+  }
+  __syncthreads();
+  for (int t = threadIdx.x; t < NACC * K; t += NT) {
+    double s = 0.0;
+#pragma unroll
+    for (int w = 0; w < NWARP; ++w) s += smem[w * NACC * K + t];
+    out[t] = s;
+  }
+}
+
+// "Last CTA done" election.  All threads must call; returns true in every thread of the last CTA to arrive.
+// The partial table written before the call is visible to the elected CTA.
+__device__ __forceinline__ bool elect_last_cta(unsigned int* counter) {
+  __shared__ int s_last;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned int t = atomicAdd(counter, 1u);
+    s_last = (t == gridDim.x - 1);
+    if (s_last) *counter = 0u;  // re-arm for the next launch (stream ordered)
+  }
+  __syncthreads();
+  if (s_last) __threadfence();
+  return s_last != 0;
+}
+
+}  // namespace slq

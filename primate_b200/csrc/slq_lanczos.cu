@@ -1,0 +1,763 @@
+// Probe-blocked Lanczos driver for sm_100a.
+//
+// Restates, for a block of k probes at once, the reference's Paige-A27 recurrence
+// (src/primate/include/lanczos.h:92-149) and its modified-Gram-Schmidt re-projection (lanczos.h:43-66):
+//
+//   w  = A q_c - beta_j q_p          alpha_j = <q_c, w>          (kernel "A": CSR SpMM fused with both)
+//   v  = w - alpha_j q_c             [MGS against stored q's]    beta_{j+1} = ||v||   (kernel(s) "axpy")
+//   q_n = v / beta_{j+1}                                          (never materialised: see below)
+//
+// Layout: every Lanczos vector block is an n x K row-major panel (probe-minor).  Vectors are kept
+// UN-normalised (u = beta * q) with a per-probe reciprocal scale, so the division by beta_{j+1} -- which
+// needs a grid-wide reduction first -- costs no extra pass over HBM: consumers multiply by the scale on load.
+// Grid-wide reductions (alpha, beta, MGS coefficients) are deterministic: per-CTA partials in a table, summed
+// in fixed order by the last CTA to finish, which also runs the scalar recurrence bookkeeping (early break
+// mask, lanczos.h:140).  Dots and norms accumulate in fp64 for both fp32 and fp64 panels.
+#include <cmath>
+#include <limits>
+#include <vector>
+
+#include "slq_internal.cuh"
+
+namespace slq {
+
+constexpr int MAXK = 64;
+
+// Per-block scalar state in device memory (one per workspace).
+struct LzScal {
+  double coef[MAXK];   // pending "v -= coef * u" coefficient (already multiplied by the column's scale)
+  double beta[MAXK];   // beta_j of the current step (rounded to the panel dtype)
+  double xnorm2[MAXK];
+  int active[MAXK];    // 0 once the probe hit the early break (lanczos.h:140) or finished
+  int steps[MAXK];
+  unsigned int counter;
+};
+
+struct StepOut {   // where the finalising CTA records the tridiagonal entries
+  void* alpha;     // k x ld
+  void* beta;      // k x ld
+  int ld;
+  int j;           // step index
+  int deg;
+  double tol;      // sqrt(n) * rtol
+  double orth_tol; // 2 eps sqrt(n)
+};
+
+// Sum column `t` of the per-CTA partial table in a fixed order using the whole CTA.
+template <int NS>
+__device__ __forceinline__ void reduce_partials(const double* partial, int ncta, double* smem /* NT */, double* result /* NS, smem */) {
+  constexpr int NCH = NT / NS > 0 ? NT / NS : 1;
+  const int t = threadIdx.x;
+  if (NS <= NT) {
+    const int slot = t % NS, ch = t / NS;
+    double s = 0.0;
+    if (ch < NCH)
+      for (int c = ch; c < ncta; c += NCH) s += __ldcg(partial + (size_t)c * NS + slot);
+    smem[t] = s;
+    __syncthreads();
+    if (t < NS) {
+      double r = 0.0;
+#pragma unroll
+      for (int c = 0; c < NCH; ++c) r += smem[c * NS + t];
+      result[t] = r;
+    }
+    __syncthreads();
+  }
+}
+
+template <typename T>
+__device__ __forceinline__ double round_to(double x) {
+  return (double)(T)x;
+}
+
+// ---- finalisers (run by every thread of the last CTA) ---------------------------------------------------
+enum Fin { FIN_INIT = 0, FIN_ALPHA = 1, FIN_BETA = 2, FIN_COEF = 3 };
+
+template <typename T, int K, int FIN>
+__device__ __forceinline__ void finalize(const double* partial, LzScal* sc, double* scale_a, const double* scale_b,
+                                         const StepOut& so, double* smem) {
+  constexpr int NACC = (FIN == FIN_COEF) ? 2 : 1;
+  constexpr int NS = NACC * K;
+  __shared__ double s_res[2 * MAXK];
+  reduce_partials<NS>(partial, gridDim.x, smem, s_res);
+  const int t = threadIdx.x;
+  if (t < K) {
+    if (FIN == FIN_INIT) {
+      // q_0 = x / ||x||  (Eigen normalized(): untouched when the norm is zero), lanczos.h:120
+      double z = s_res[t];
+      sc->xnorm2[t] = z;
+      double nrm = round_to<T>(sqrt(round_to<T>(z)));
+      scale_a[t] = (z > 0.0) ? round_to<T>(1.0 / nrm) : 1.0;
+      sc->beta[t] = 0.0;
+      sc->coef[t] = 0.0;
+      sc->active[t] = 1;
+      sc->steps[t] = 0;
+    } else if (FIN == FIN_ALPHA) {
+      // alpha_j = <q_c, w>; pending update v = w - alpha_j q_c  (lanczos.h:129-130)
+      double a = round_to<T>(s_res[t]);
+      if (sc->active[t]) reinterpret_cast<T*>(so.alpha)[(size_t)t * so.ld + so.j] = (T)a;
+      sc->coef[t] = round_to<T>(a * scale_b[t]);
+    } else if (FIN == FIN_BETA) {
+      // beta_{j+1} = ||v||; early break when < sqrt(n) rtol or at the last step (lanczos.h:139-143)
+      double b = round_to<T>(sqrt(s_res[t]));
+      if (sc->active[t]) {
+        reinterpret_cast<T*>(so.beta)[(size_t)t * so.ld + so.j + 1] = (T)b;
+        sc->steps[t] = so.j + 1;
+        if (b < so.tol || so.j + 1 == so.deg) sc->active[t] = 0;
+      }
+      sc->beta[t] = b;
+      scale_a[t] = round_to<T>(1.0 / b);
+      sc->coef[t] = 0.0;
+    } else {  // FIN_COEF: one modified-Gram-Schmidt projection coefficient (lanczos.h:59-64)
+      double r = scale_b[t];
+      double u_norm = round_to<T>(s_res[t] * r * r);
+      double s_proj = round_to<T>(s_res[K + t] * r);
+      bool take = (u_norm > so.orth_tol) && (fabs(s_proj) > so.orth_tol);
+      sc->coef[t] = take ? round_to<T>(round_to<T>(s_proj / u_norm) * r) : 0.0;
+    }
+  }
+}
+
+// ---- kernel: ||x||^2 of the start block --------------------------------------------------------------------
+template <typename T, int K>
+__global__ void __launch_bounds__(NT) k_init(int64_t n, const T* __restrict__ x, LzScal* sc, double* scale0, double* partial,
+                                              StepOut so) {
+  using M = BlockMap<T, K>;
+  constexpr int V = M::V, LPR = M::LPR;
+  __shared__ double smem[NT > NWARP * K ? NT : NWARP * K];
+  double acc[1][V];
+#pragma unroll
+  for (int i = 0; i < V; ++i) acc[0][i] = 0.0;
+  const int64_t nvec = n * LPR;
+  for (int64_t e = (int64_t)blockIdx.x * NT + threadIdx.x; e < nvec; e += (int64_t)gridDim.x * NT) {
+    Pack<T, V> xv = ld_pack<T, V, LD_DEFAULT>(x + e * V);
+#pragma unroll
+    for (int i = 0; i < V; ++i) acc[0][i] += (double)xv.v[i] * (double)xv.v[i];
+  }
+  cta_reduce_slots<K, V, LPR, 1>(acc, partial + (size_t)blockIdx.x * K, smem);
+  if (elect_last_cta(&sc->counter)) finalize<T, K, FIN_INIT>(partial, sc, scale0, nullptr, so, smem);
+}
+
+// ---- kernel A: w = (A u_c) r_c - beta_j (u_p r_p);  alpha partials ----------------------------------------
+// CSR SpMM over the probe block fused with the first half of the three-term recurrence.  One thread owns V
+// adjacent probes of a row (16-byte vector gathers); LPR threads cover a row; a CTA sweeps tiles of
+// consecutive rows assigned round-robin so that all CTAs advance through the matrix as one front (keeps the
+// gathered rows of u_c resident in L1/L2 while neighbours re-use them).
+template <typename T, int K, bool FIRST, bool FUSED_CSR>
+__global__ void __launch_bounds__(NT)
+    k_stepA(int64_t n, const int32_t* __restrict__ rowptr, const int32_t* __restrict__ colidx, const T* __restrict__ vals,
+            const T* __restrict__ uc, const T* __restrict__ up, T* __restrict__ w, LzScal* sc, const double* scale_c,
+            const double* scale_p, double* partial, StepOut so) {
+  using M = BlockMap<T, K>;
+  constexpr int V = M::V, LPR = M::LPR;
+  constexpr int RPC = NT / LPR;  // rows per CTA pass
+  constexpr int PASSES = 4;
+  constexpr int TILE = RPC * PASSES;
+  __shared__ double smem[NT > NWARP * K ? NT : NWARP * K];
+
+  const int sub = threadIdx.x % LPR, rloc = threadIdx.x / LPR;
+  const int slot = sub * V;
+  T rc[V], brp[V];
+#pragma unroll
+  for (int i = 0; i < V; ++i) {
+    rc[i] = (T)scale_c[slot + i];
+    brp[i] = FIRST ? (T)0 : (T)(sc->beta[slot + i]) * (T)scale_p[slot + i];
+  }
+  double acc_a[1][V];
+#pragma unroll
+  for (int i = 0; i < V; ++i) acc_a[0][i] = 0.0;
+
+  const int64_t ntiles = (n + TILE - 1) / TILE;
+  for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const int64_t row0 = tile * TILE;
+#pragma unroll
+    for (int ps = 0; ps < PASSES; ++ps) {
+      const int64_t r = row0 + ps * RPC + rloc;
+      if (r < n) {
+        T acc[V];
+        if (FUSED_CSR) {
+#pragma unroll
+          for (int i = 0; i < V; ++i) acc[i] = (T)0;
+          const int s = __ldg(rowptr + r), e = __ldg(rowptr + r + 1);
+#pragma unroll 4
+          for (int i = s; i < e; ++i) {
+            const int64_t c = __ldg(colidx + i);
+            const T a = __ldg(vals + i);
+            Pack<T, V> xv = ld_pack<T, V, LD_READONLY>(uc + c * K + slot);
+#pragma unroll
+            for (int q = 0; q < V; ++q) acc[q] = fma(a, xv.v[q], acc[q]);
+          }
+        } else {
+          Pack<T, V> yv = ld_pack<T, V, LD_DEFAULT>(w + r * K + slot);  // y = A u_c computed by the operator
+#pragma unroll
+          for (int q = 0; q < V; ++q) acc[q] = yv.v[q];
+        }
+        Pack<T, V> qc = ld_pack<T, V, LD_READONLY>(uc + r * K + slot);
+        Pack<T, V> wv;
+        if (FIRST) {
+#pragma unroll
+          for (int q = 0; q < V; ++q) wv.v[q] = acc[q] * rc[q];
+        } else {
+          Pack<T, V> pv = ld_pack<T, V, LD_STREAM>(up + r * K + slot);
+#pragma unroll
+          for (int q = 0; q < V; ++q) wv.v[q] = acc[q] * rc[q] - brp[q] * pv.v[q];
+        }
+        st_pack<T, V, false>(w + r * K + slot, wv);
+#pragma unroll
+        for (int q = 0; q < V; ++q) acc_a[0][q] += (double)(qc.v[q] * rc[q]) * (double)wv.v[q];
+      }
+    }
+  }
+  cta_reduce_slots<K, V, LPR, 1>(acc_a, partial + (size_t)blockIdx.x * K, smem);
+  if (elect_last_cta(&sc->counter)) finalize<T, K, FIN_ALPHA>(partial, sc, nullptr, scale_c, so, smem);
+}
+
+// ---- kernel "axpy": v -= coef * u1, then either ||v||^2 or the next projection's dots ------------------------
+enum AxpyMode { AX_NORM = 0, AX_DOT_SAME = 1, AX_DOT_OTHER = 2 };
+
+template <typename T, int K, int MODE>
+__global__ void __launch_bounds__(NT) k_axpy(int64_t n, T* __restrict__ v, const T* __restrict__ u1, const T* __restrict__ u2,
+                                              LzScal* sc, double* scale_v, const double* scale_u2, double* partial, StepOut so) {
+  using M = BlockMap<T, K>;
+  constexpr int V = M::V, LPR = M::LPR;
+  constexpr int NACC = (MODE == AX_NORM) ? 1 : 2;
+  __shared__ double smem[NT > NWARP * NACC * K ? NT : NWARP * NACC * K];
+  const int slot = (threadIdx.x % LPR) * V;
+  T cf[V];
+#pragma unroll
+  for (int i = 0; i < V; ++i) cf[i] = (T)sc->coef[slot + i];
+  double acc[NACC][V];
+#pragma unroll
+  for (int a = 0; a < NACC; ++a)
+#pragma unroll
+    for (int i = 0; i < V; ++i) acc[a][i] = 0.0;
+
+  const int64_t nvec = n * LPR;
+  const int64_t stride = (int64_t)gridDim.x * NT;
+  for (int64_t e = (int64_t)blockIdx.x * NT + threadIdx.x; e < nvec; e += stride) {
+    Pack<T, V> vv = ld_pack<T, V, LD_STREAM>(v + e * V);
+    Pack<T, V> a1 = ld_pack<T, V, LD_DEFAULT>(u1 + e * V);
+    Pack<T, V> a2;
+    if (MODE == AX_DOT_OTHER) a2 = ld_pack<T, V, LD_DEFAULT>(u2 + e * V);
+#pragma unroll
+    for (int q = 0; q < V; ++q) vv.v[q] = vv.v[q] - cf[q] * a1.v[q];
+    st_pack<T, V, false>(v + e * V, vv);
+#pragma unroll
+    for (int q = 0; q < V; ++q) {
+      if (MODE == AX_NORM) {
+        acc[0][q] += (double)vv.v[q] * (double)vv.v[q];
+      } else {
+        const T uu = (MODE == AX_DOT_SAME) ? a1.v[q] : a2.v[q];
+        acc[0][q] += (double)uu * (double)uu;
+        acc[1][q] += (double)vv.v[q] * (double)uu;
+      }
+    }
+  }
+  cta_reduce_slots<K, V, LPR, NACC>(acc, partial + (size_t)blockIdx.x * NACC * K, smem);
+  if (elect_last_cta(&sc->counter)) {
+    if (MODE == AX_NORM)
+      finalize<T, K, FIN_BETA>(partial, sc, scale_v, nullptr, so, smem);
+    else
+      finalize<T, K, FIN_COEF>(partial, sc, nullptr, scale_u2, so, smem);
+  }
+}
+
+// ---- kernel: export one normalised Lanczos vector block into the caller's basis ----------------------------
+template <typename T, int K>
+__global__ void __launch_bounds__(NT) k_export(int64_t n, const T* __restrict__ u, const double* scale, const LzScal* sc, int m,
+                                                T* __restrict__ out) {
+  using M = BlockMap<T, K>;
+  constexpr int V = M::V, LPR = M::LPR;
+  const int slot = (threadIdx.x % LPR) * V;
+  T r[V];
+#pragma unroll
+  for (int i = 0; i < V; ++i) r[i] = (m < sc->steps[slot + i] || m == 0) ? (T)scale[slot + i] : (T)0;
+  const int64_t nvec = n * LPR;
+  for (int64_t e = (int64_t)blockIdx.x * NT + threadIdx.x; e < nvec; e += (int64_t)gridDim.x * NT) {
+    Pack<T, V> x = ld_pack<T, V, LD_STREAM>(u + e * V);
+#pragma unroll
+    for (int q = 0; q < V; ++q) x.v[q] = (r[q] != (T)0) ? x.v[q] * r[q] : (T)0;
+    st_pack<T, V, true>(out + e * V, x);
+  }
+}
+
+__global__ void k_copy_steps(const LzScal* sc, int k, int32_t* steps, double* xnorm2) {
+  int t = threadIdx.x;
+  if (t < k) {
+    if (steps) steps[t] = sc->steps[t];
+    if (xnorm2) xnorm2[t] = sc->xnorm2[t];
+  }
+}
+
+// ---- dense symmetric operator: Y = A X ------------------------------------------------------------------------
+// Shared-memory tiled panel product (A tile TR x TC staged once per CTA, X chunk TC x K staged alongside).
+template <typename T, int K>
+__global__ void __launch_bounds__(NT) k_dense_matmat(int64_t n, const T* __restrict__ A, int64_t ld, const T* __restrict__ X,
+                                                      T* __restrict__ Y) {
+  using M = BlockMap<T, K>;
+  constexpr int V = M::V, LPR = M::LPR;
+  constexpr int RPC = NT / LPR;
+  constexpr int RR = RPC >= 128 ? 1 : (128 / RPC > 8 ? 8 : 128 / RPC);
+  constexpr int TR = RPC * RR;
+  constexpr int TC = 16;
+  __shared__ T As[TR][TC + 1];
+  __shared__ T Xs[TC][K];
+  const int sub = threadIdx.x % LPR, rloc = threadIdx.x / LPR;
+  const int slot = sub * V;
+  const int64_t row0 = (int64_t)blockIdx.x * TR;
+  T acc[RR][V];
+#pragma unroll
+  for (int a = 0; a < RR; ++a)
+#pragma unroll
+    for (int q = 0; q < V; ++q) acc[a][q] = (T)0;
+  for (int64_t c0 = 0; c0 < n; c0 += TC) {
+    for (int idx = threadIdx.x; idx < TR * TC; idx += NT) {
+      const int rr = idx / TC, cc = idx % TC;
+      const int64_t r = row0 + rr, c = c0 + cc;
+      As[rr][cc] = (r < n && c < n) ? A[r * ld + c] : (T)0;
+    }
+    for (int idx = threadIdx.x; idx < TC * K; idx += NT) {
+      const int cc = idx / K, p = idx % K;
+      const int64_t c = c0 + cc;
+      Xs[cc][p] = (c < n) ? X[c * K + p] : (T)0;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int cc = 0; cc < TC; ++cc) {
+      T xv[V];
+#pragma unroll
+      for (int q = 0; q < V; ++q) xv[q] = Xs[cc][slot + q];
+#pragma unroll
+      for (int a = 0; a < RR; ++a) {
+        const T av = As[rloc + a * RPC][cc];
+#pragma unroll
+        for (int q = 0; q < V; ++q) acc[a][q] = fma(av, xv[q], acc[a][q]);
+      }
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int a = 0; a < RR; ++a) {
+    const int64_t r = row0 + rloc + a * RPC;
+    if (r < n) {
+      Pack<T, V> o;
+#pragma unroll
+      for (int q = 0; q < V; ++q) o.v[q] = acc[a][q];
+      st_pack<T, V, false>(Y + r * K + slot, o);
+    }
+  }
+}
+
+// ---- plain CSR SpMM: Y = A X (slq_op_matmat; the roofline probe for the gather itself) -----------------------
+template <typename T, int K>
+__global__ void __launch_bounds__(NT) k_csr_matmat(int64_t n, const int32_t* __restrict__ rowptr, const int32_t* __restrict__ colidx,
+                                                    const T* __restrict__ vals, const T* __restrict__ X, T* __restrict__ Y) {
+  using M = BlockMap<T, K>;
+  constexpr int V = M::V, LPR = M::LPR;
+  constexpr int RPC = NT / LPR;
+  constexpr int PASSES = 4;
+  constexpr int TILE = RPC * PASSES;
+  const int sub = threadIdx.x % LPR, rloc = threadIdx.x / LPR;
+  const int slot = sub * V;
+  const int64_t ntiles = (n + TILE - 1) / TILE;
+  for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+#pragma unroll
+    for (int ps = 0; ps < PASSES; ++ps) {
+      const int64_t r = tile * TILE + ps * RPC + rloc;
+      if (r < n) {
+        T acc[V];
+#pragma unroll
+        for (int i = 0; i < V; ++i) acc[i] = (T)0;
+        const int s = __ldg(rowptr + r), e = __ldg(rowptr + r + 1);
+#pragma unroll 4
+        for (int i = s; i < e; ++i) {
+          const int64_t c = __ldg(colidx + i);
+          const T a = __ldg(vals + i);
+          Pack<T, V> xv = ld_pack<T, V, LD_READONLY>(X + c * K + slot);
+#pragma unroll
+          for (int q = 0; q < V; ++q) acc[q] = fma(a, xv.v[q], acc[q]);
+        }
+        Pack<T, V> o;
+#pragma unroll
+        for (int q = 0; q < V; ++q) o.v[q] = acc[q];
+        st_pack<T, V, true>(Y + r * K + slot, o);
+      }
+    }
+  }
+}
+
+// ---- layout helpers ---------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void k_cols_to_block(const T* __restrict__ cols, int64_t n, int k, T* __restrict__ X) {
+  // cols: k contiguous columns of length n (F-ordered (n,k)); X: n x k row-major.  32x32 smem transpose tiles.
+  __shared__ T tile[32][33];
+  const int64_t r0 = (int64_t)blockIdx.x * 32;
+  const int p0 = blockIdx.y * 32;
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int p = p0 + i;
+    const int64_t r = r0 + threadIdx.x;
+    tile[i][threadIdx.x] = (p < k && r < n) ? cols[(int64_t)p * n + r] : (T)0;
+  }
+  __syncthreads();
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int64_t r = r0 + i;
+    const int p = p0 + threadIdx.x;
+    if (r < n && p < k) X[r * k + p] = tile[threadIdx.x][i];
+  }
+}
+
+template <typename T>
+__global__ void k_block_to_cols(const T* __restrict__ X, int64_t n, int k, T* __restrict__ cols) {
+  __shared__ T tile[32][33];
+  const int64_t r0 = (int64_t)blockIdx.x * 32;
+  const int p0 = blockIdx.y * 32;
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int64_t r = r0 + i;
+    const int p = p0 + threadIdx.x;
+    tile[i][threadIdx.x] = (r < n && p < k) ? X[r * k + p] : (T)0;
+  }
+  __syncthreads();
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int p = p0 + i;
+    const int64_t r = r0 + threadIdx.x;
+    if (p < k && r < n) cols[(int64_t)p * n + r] = tile[threadIdx.x][i];
+  }
+}
+
+// ---- host side ------------------------------------------------------------------------------------------------------
+struct Grid {
+  int stream_ctas;  // persistent grid for the streaming kernels
+};
+
+static int grid_for(int64_t work_items /* vector elements or rows */, int per_cta) {
+  int sms = sm_count();
+  if (sms <= 0) return -1;
+  int64_t need = (work_items + per_cta - 1) / per_cta;
+  int64_t cap = (int64_t)sms * 4;  // 4 resident CTAs of 256 threads per SM
+  if (need < 1) need = 1;
+  return (int)(need < cap ? need : cap);
+}
+
+struct Workspace {
+  char* base;
+  size_t panel_bytes;
+  int npanel;
+  LzScal* sc;
+  double* scales;   // (npanel + 1) x MAXK
+  double* partial;  // max_ctas x 2 x MAXK
+};
+
+static size_t ws_layout(int64_t n, int k, int ncv, int dtype, Workspace* ws, char* base) {
+  size_t panel = align_up((size_t)n * k * dtype_size(dtype), 256);
+  size_t off = 0;
+  size_t panels_off = off;
+  off += panel * (size_t)ncv;
+  size_t sc_off = off;
+  off += align_up(sizeof(LzScal), 256);
+  size_t scales_off = off;
+  off += align_up(sizeof(double) * MAXK * (size_t)(ncv + 1), 256);
+  size_t partial_off = off;
+  int sms = sm_count();
+  if (sms <= 0) sms = 148;
+  off += align_up(sizeof(double) * 2 * MAXK * (size_t)sms * 4, 256);
+  if (ws) {
+    ws->base = base + panels_off;
+    ws->panel_bytes = panel;
+    ws->npanel = ncv;
+    ws->sc = reinterpret_cast<LzScal*>(base + sc_off);
+    ws->scales = reinterpret_cast<double*>(base + scales_off);
+    ws->partial = reinterpret_cast<double*>(base + partial_off);
+  }
+  return off;
+}
+
+template <typename T, int K>
+static int op_apply(slq_op* op, const T* X, T* Y, cudaStream_t st) {
+  const int64_t n = op->n;
+  if (op->kind == OP_CSR) {
+    constexpr int RPC = NT / BlockMap<T, K>::LPR;
+    int g = grid_for(n, RPC * 4);
+    k_csr_matmat<T, K><<<g, NT, 0, st>>>(n, op->rowptr, op->colidx, (const T*)op->vals, X, Y);
+    SLQ_LAUNCH_CHECK();
+  } else if (op->kind == OP_DENSE) {
+    constexpr int RPC = NT / BlockMap<T, K>::LPR;
+    constexpr int RR = RPC >= 128 ? 1 : (128 / RPC > 8 ? 8 : 128 / RPC);
+    int64_t g = (n + RPC * RR - 1) / (RPC * RR);
+    k_dense_matmat<T, K><<<(unsigned)g, NT, 0, st>>>(n, (const T*)op->dense, op->ld, X, Y);
+    SLQ_LAUNCH_CHECK();
+  } else {
+    int rc = op->fn(op->ctx, X, Y, n, K, op->dtype, (slq_stream)st);
+    if (rc != 0) return fail(SLQ_ERR_CALLBACK, "operator callback returned %d", rc);
+  }
+  return SLQ_OK;
+}
+
+template <typename T, int K>
+static int lanczos_impl(slq_op* op, T* X, int deg, double rtol, int orth, int ncv, T* alpha, T* beta, int32_t* steps,
+                        double* xnorm2, T* Qout, char* wsbase, cudaStream_t st) {
+  const int64_t n = op->n;
+  using M = BlockMap<T, K>;
+  Workspace ws;
+  ws_layout(n, K, ncv, op->dtype, &ws, wsbase);
+  const int ld = deg + 1;
+  SLQ_CUDA(cudaMemsetAsync(alpha, 0, sizeof(T) * (size_t)K * ld, st));
+  SLQ_CUDA(cudaMemsetAsync(beta, 0, sizeof(T) * (size_t)K * ld, st));
+  SLQ_CUDA(cudaMemsetAsync(ws.sc, 0, sizeof(LzScal), st));
+
+  // physical panels: 0 = caller's X, 1..ncv = workspace
+  std::vector<T*> phys(ncv + 1);
+  phys[0] = X;
+  for (int i = 0; i < ncv; ++i) phys[i + 1] = reinterpret_cast<T*>(ws.base + ws.panel_bytes * (size_t)i);
+  auto scale_of = [&](int ph) { return ws.scales + (size_t)ph * MAXK; };
+  std::vector<int> slot_phys(ncv, -1), slot_vec(ncv, -1);  // logical column -> physical panel, Lanczos vector index
+  std::vector<int> free_list;
+  for (int i = ncv; i >= 1; --i) free_list.push_back(i);
+  slot_phys[0] = 0;
+  slot_vec[0] = 0;
+
+  StepOut so;
+  so.alpha = alpha;
+  so.beta = beta;
+  so.ld = ld;
+  so.j = 0;
+  so.deg = deg;
+  so.tol = (double)(T)(std::sqrt((double)n) * (double)(T)rtol);                          // lanczos.h:110 (F residual_tol)
+  so.orth_tol = 2.0 * (double)std::numeric_limits<T>::epsilon() * std::sqrt((double)n);  // lanczos.h:53 (a double)
+
+  const int g_vec = grid_for(n * M::LPR, NT * 4);
+  const int g_row = grid_for(n, (NT / M::LPR) * 4);
+  if (g_vec <= 0) return fail(SLQ_ERR_CUDA, "no CUDA device");
+
+  k_init<T, K><<<g_vec, NT, 0, st>>>(n, X, ws.sc, scale_of(0), ws.partial, so);
+  SLQ_LAUNCH_CHECK();
+
+  int pos[3] = {ncv - 1, 0, 1 % ncv};
+  int F = free_list.back();
+  free_list.pop_back();
+  for (int j = 0; j < deg; ++j) {
+    const int p = pos[0], c = pos[1], nx = pos[2];
+    so.j = j;
+    const int pc = slot_phys[c];
+    const int pp = (j == 0) ? -1 : slot_phys[p];
+    T* w = phys[F];
+    const bool first = (pp < 0);
+    const T* upp = first ? phys[pc] : phys[pp];
+    const double* scp = first ? scale_of(pc) : scale_of(pp);
+    if (op->kind == OP_CSR) {
+      if (first)
+        k_stepA<T, K, true, true><<<g_row, NT, 0, st>>>(n, op->rowptr, op->colidx, (const T*)op->vals, phys[pc], upp, w, ws.sc,
+                                                        scale_of(pc), scp, ws.partial, so);
+      else
+        k_stepA<T, K, false, true><<<g_row, NT, 0, st>>>(n, op->rowptr, op->colidx, (const T*)op->vals, phys[pc], upp, w, ws.sc,
+                                                         scale_of(pc), scp, ws.partial, so);
+    } else {
+      int rc = op_apply<T, K>(op, phys[pc], w, st);
+      if (rc != SLQ_OK) return rc;
+      if (first)
+        k_stepA<T, K, true, false><<<g_row, NT, 0, st>>>(n, nullptr, nullptr, nullptr, phys[pc], upp, w, ws.sc, scale_of(pc), scp,
+                                                         ws.partial, so);
+      else
+        k_stepA<T, K, false, false><<<g_row, NT, 0, st>>>(n, nullptr, nullptr, nullptr, phys[pc], upp, w, ws.sc, scale_of(pc), scp,
+                                                          ws.partial, so);
+    }
+    SLQ_LAUNCH_CHECK();
+
+    // columns visited by the re-projection: c, c-1, ... cyclically, `orth` of them; unwritten (zero) columns are
+    // skipped exactly as the reference's u_norm > tol guard skips them (lanczos.h:58-64, fresh basis).
+    std::vector<int> visit;
+    for (int t = 0, i = c; t < orth; ++t, i = ((i - 1) % ncv + ncv) % ncv)
+      if (slot_phys[i] >= 0) visit.push_back(slot_phys[i]);
+    if (visit.empty()) {
+      k_axpy<T, K, AX_NORM><<<g_vec, NT, 0, st>>>(n, w, phys[pc], nullptr, ws.sc, scale_of(F), nullptr, ws.partial, so);
+      SLQ_LAUNCH_CHECK();
+    } else {
+      // visit[0] is always the current column: fuse "v = w - alpha q_c" with the first projection's dots
+      k_axpy<T, K, AX_DOT_SAME><<<g_vec, NT, 0, st>>>(n, w, phys[pc], nullptr, ws.sc, nullptr, scale_of(visit[0]), ws.partial, so);
+      SLQ_LAUNCH_CHECK();
+      for (size_t m = 1; m < visit.size(); ++m) {
+        k_axpy<T, K, AX_DOT_OTHER><<<g_vec, NT, 0, st>>>(n, w, phys[visit[m - 1]], phys[visit[m]], ws.sc, nullptr,
+                                                         scale_of(visit[m]), ws.partial, so);
+        SLQ_LAUNCH_CHECK();
+      }
+      k_axpy<T, K, AX_NORM><<<g_vec, NT, 0, st>>>(n, w, phys[visit.back()], nullptr, ws.sc, scale_of(F), nullptr, ws.partial, so);
+      SLQ_LAUNCH_CHECK();
+    }
+    if (j + 1 < deg) {  // Q.col(n) = v / beta  (lanczos.h:143): the panel just becomes column `nx`
+      const int old = slot_phys[nx];
+      slot_phys[nx] = F;
+      slot_vec[nx] = j + 1;
+      if (old >= 0) {
+        F = old;
+      } else {
+        if (free_list.empty()) return fail(SLQ_ERR_ARG, "internal: out of Lanczos panels");
+        F = free_list.back();
+        free_list.pop_back();
+      }
+      pos[0] = c;
+      pos[1] = nx;
+      pos[2] = (j + 2) % ncv;
+    }
+  }
+  if (Qout) {
+    SLQ_CUDA(cudaMemsetAsync(Qout, 0, sizeof(T) * (size_t)n * K * ncv, st));
+    for (int s = 0; s < ncv; ++s) {
+      if (slot_phys[s] < 0) continue;
+      k_export<T, K><<<g_vec, NT, 0, st>>>(n, phys[slot_phys[s]], scale_of(slot_phys[s]), ws.sc, slot_vec[s],
+                                           Qout + (size_t)s * n * K);
+      SLQ_LAUNCH_CHECK();
+    }
+  }
+  if (steps || xnorm2) {
+    k_copy_steps<<<1, MAXK, 0, st>>>(ws.sc, K, steps, xnorm2);
+    SLQ_LAUNCH_CHECK();
+  }
+  return SLQ_OK;
+}
+
+#define SLQ_DISPATCH_K(T, k, CALL)                        \
+  switch (k) {                                            \
+    case 1: { constexpr int KK = 1; return CALL; }        \
+    case 2: { constexpr int KK = 2; return CALL; }        \
+    case 4: { constexpr int KK = 4; return CALL; }        \
+    case 8: { constexpr int KK = 8; return CALL; }        \
+    case 16: { constexpr int KK = 16; return CALL; }      \
+    case 32: { constexpr int KK = 32; return CALL; }      \
+    case 64: { constexpr int KK = 64; return CALL; }      \
+    default: return fail(SLQ_ERR_ARG, "block width k=%d must be a power of two in [1,64]", k); \
+  }
+
+template <typename T>
+static int lanczos_dispatch(slq_op* op, void* X, int k, int deg, double rtol, int orth, int ncv, void* alpha, void* beta,
+                            int32_t* steps, double* xnorm2, void* Q, char* ws, cudaStream_t st) {
+  SLQ_DISPATCH_K(T, k, (lanczos_impl<T, KK>(op, (T*)X, deg, rtol, orth, ncv, (T*)alpha, (T*)beta, steps, xnorm2, (T*)Q, ws, st)));
+}
+
+template <typename T>
+static int matmat_dispatch(slq_op* op, const void* X, void* Y, int k, cudaStream_t st) {
+  SLQ_DISPATCH_K(T, k, (op_apply<T, KK>(op, (const T*)X, (T*)Y, st)));
+}
+
+}  // namespace slq
+
+using namespace slq;
+
+extern "C" {
+
+int slq_csr_create(int64_t n, int64_t nnz, const int32_t* rowptr_dev, const int32_t* colidx_dev, const void* vals_dev, int dtype,
+                   slq_op** out) {
+  SLQ_REQUIRE(out != nullptr, "out is NULL");
+  SLQ_REQUIRE(n > 0 && nnz >= 0, "invalid shape n=%lld nnz=%lld", (long long)n, (long long)nnz);
+  SLQ_REQUIRE(nnz < (int64_t)INT32_MAX, "nnz=%lld does not fit int32 row pointers", (long long)nnz);
+  SLQ_REQUIRE(n < (int64_t)INT32_MAX, "n=%lld does not fit int32 column indices", (long long)n);
+  SLQ_REQUIRE(dtype == SLQ_F32 || dtype == SLQ_F64, "Only 32- or 64-bit floats are supported.");
+  SLQ_REQUIRE(rowptr_dev && (nnz == 0 || (colidx_dev && vals_dev)), "NULL CSR array");
+  slq_op* op = new slq_op();
+  op->kind = OP_CSR;
+  op->dtype = dtype;
+  op->n = n;
+  op->nnz = nnz;
+  op->rowptr = rowptr_dev;
+  op->colidx = colidx_dev;
+  op->vals = vals_dev;
+  *out = op;
+  return SLQ_OK;
+}
+
+int slq_dense_create(int64_t n, const void* A_dev, int64_t ld, int dtype, slq_op** out) {
+  SLQ_REQUIRE(out != nullptr, "out is NULL");
+  SLQ_REQUIRE(n > 0 && ld >= n && A_dev, "invalid dense operator (n=%lld, ld=%lld)", (long long)n, (long long)ld);
+  SLQ_REQUIRE(dtype == SLQ_F32 || dtype == SLQ_F64, "Only 32- or 64-bit floats are supported.");
+  slq_op* op = new slq_op();
+  op->kind = OP_DENSE;
+  op->dtype = dtype;
+  op->n = n;
+  op->nnz = n * n;
+  op->dense = A_dev;
+  op->ld = ld;
+  *out = op;
+  return SLQ_OK;
+}
+
+int slq_callback_create(int64_t n, int dtype, slq_matmat_fn fn, void* ctx, slq_op** out) {
+  SLQ_REQUIRE(out != nullptr, "out is NULL");
+  SLQ_REQUIRE(n > 0, "invalid shape");
+  SLQ_REQUIRE(fn != nullptr, "Supplied object is missing 'matvec' attribute.");  // pylinop.h:24
+  SLQ_REQUIRE(dtype == SLQ_F32 || dtype == SLQ_F64, "Only 32- or 64-bit floats are supported.");
+  slq_op* op = new slq_op();
+  op->kind = OP_CALLBACK;
+  op->dtype = dtype;
+  op->n = n;
+  op->nnz = 0;
+  op->fn = fn;
+  op->ctx = ctx;
+  *out = op;
+  return SLQ_OK;
+}
+
+int slq_op_destroy(slq_op* op) {
+  delete op;
+  return SLQ_OK;
+}
+int64_t slq_op_rows(const slq_op* op) { return op ? op->n : -1; }
+int slq_op_dtype(const slq_op* op) { return op ? op->dtype : -1; }
+int64_t slq_op_nnz(const slq_op* op) { return op ? op->nnz : -1; }
+
+int slq_op_matmat(slq_op* op, const void* X_dev, void* Y_dev, int k, slq_stream stream) {
+  SLQ_REQUIRE(op && X_dev && Y_dev, "NULL argument");
+  SLQ_REQUIRE(X_dev != Y_dev, "X and Y must not alias");
+  if (sm_count() <= 0) return fail(SLQ_ERR_CUDA, "no CUDA device");
+  cudaStream_t st = (cudaStream_t)stream;
+  return op->dtype == SLQ_F64 ? matmat_dispatch<double>(op, X_dev, Y_dev, k, st) : matmat_dispatch<float>(op, X_dev, Y_dev, k, st);
+}
+
+size_t slq_lanczos_workspace_bytes(int64_t n, int k, int ncv, int dtype) {
+  if (n <= 0 || k <= 0 || ncv < 2) return 0;
+  return ws_layout(n, k, ncv, dtype, nullptr, nullptr);
+}
+
+int slq_lanczos(slq_op* op, void* X_dev, int k, int deg, double rtol, int orth, int ncv, void* alpha_dev, void* beta_dev,
+                int32_t* steps_dev, double* xnorm2_dev, void* Q_dev, void* workspace_dev, size_t workspace_bytes, slq_stream stream) {
+  SLQ_REQUIRE(op && X_dev && alpha_dev && beta_dev && workspace_dev, "NULL argument");
+  SLQ_REQUIRE(deg > 0, "Number of steps must be positive!");  // lanczos.py:81
+  SLQ_REQUIRE(ncv >= 2, "ncv must be at least 2 (lanczos.h:101)");
+  SLQ_REQUIRE(orth >= 0, "orth must be non-negative at the C boundary (resolve the policy on the host)");
+  SLQ_REQUIRE(is_pow2(k) && k <= MAXK, "block width k=%d must be a power of two in [1,64]", k);
+  SLQ_REQUIRE(((uintptr_t)X_dev & 15) == 0 && ((uintptr_t)workspace_dev & 255) == 0, "X must be 16-byte and workspace 256-byte aligned");
+  if (sm_count() <= 0) return fail(SLQ_ERR_CUDA, "no CUDA device");
+  size_t need = ws_layout(op->n, k, ncv, op->dtype, nullptr, nullptr);
+  SLQ_REQUIRE(workspace_bytes >= need, "workspace too small: %zu < %zu", workspace_bytes, need);
+  cudaStream_t st = (cudaStream_t)stream;
+  return op->dtype == SLQ_F64
+             ? lanczos_dispatch<double>(op, X_dev, k, deg, rtol, orth, ncv, alpha_dev, beta_dev, steps_dev, xnorm2_dev, Q_dev,
+                                        (char*)workspace_dev, st)
+             : lanczos_dispatch<float>(op, X_dev, k, deg, rtol, orth, ncv, alpha_dev, beta_dev, steps_dev, xnorm2_dev, Q_dev,
+                                       (char*)workspace_dev, st);
+}
+
+int slq_block_from_columns(const void* cols_dev, int64_t n, int k, int dtype, void* X_dev, slq_stream stream) {
+  SLQ_REQUIRE(cols_dev && X_dev && n > 0 && k > 0, "invalid argument");
+  if (sm_count() <= 0) return fail(SLQ_ERR_CUDA, "no CUDA device");
+  dim3 grid((unsigned)((n + 31) / 32), (unsigned)((k + 31) / 32)), block(32, 8);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == SLQ_F64)
+    k_cols_to_block<double><<<grid, block, 0, st>>>((const double*)cols_dev, n, k, (double*)X_dev);
+  else
+    k_cols_to_block<float><<<grid, block, 0, st>>>((const float*)cols_dev, n, k, (float*)X_dev);
+  SLQ_LAUNCH_CHECK();
+  return SLQ_OK;
+}
+
+int slq_block_to_columns(const void* X_dev, int64_t n, int k, int dtype, void* cols_dev, slq_stream stream) {
+  SLQ_REQUIRE(cols_dev && X_dev && n > 0 && k > 0, "invalid argument");
+  if (sm_count() <= 0) return fail(SLQ_ERR_CUDA, "no CUDA device");
+  dim3 grid((unsigned)((n + 31) / 32), (unsigned)((k + 31) / 32)), block(32, 8);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == SLQ_F64)
+    k_block_to_cols<double><<<grid, block, 0, st>>>((const double*)X_dev, n, k, (double*)cols_dev);
+  else
+    k_block_to_cols<float><<<grid, block, 0, st>>>((const float*)X_dev, n, k, (float*)cols_dev);
+  SLQ_LAUNCH_CHECK();
+  return SLQ_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,280 @@
+"""Device-side engine: operator handles and block calls into libslq.  torch tensors are device buffers only.
+
+Everything here runs on the CUDA device or raises; nothing falls back to NumPy.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Any, Optional
+
+import numpy as np
+
+from . import _ffi
+
+MAX_BLOCK = 64
+
+
+def _torch():
+	import torch
+
+	if not torch.cuda.is_available():
+		raise _ffi.SlqError("primate_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback")
+	return torch
+
+
+def _stream_ptr() -> int:
+	return _torch().cuda.current_stream().cuda_stream
+
+
+def _tdtype(np_dtype):
+	torch = _torch()
+	return torch.float64 if np.dtype(np_dtype) == np.float64 else torch.float32
+
+
+def _code(np_dtype) -> int:
+	dt = np.dtype(np_dtype)
+	if dt == np.float64:
+		return _ffi.SLQ_F64
+	if dt == np.float32:
+		return _ffi.SLQ_F32
+	raise TypeError("Only 32- or 64-bit floats are supported.")  # mirrors the pybind11 overload failure
+
+
+class _DevView:
+	"""Exposes a raw device pointer through __cuda_array_interface__ so torch can view it without a copy."""
+
+	def __init__(self, ptr: int, shape: tuple, typestr: str):
+		self.__cuda_array_interface__ = {"shape": shape, "typestr": typestr, "data": (ptr, False), "version": 3, "strides": None}
+
+
+def block_sizes(count: int, kmax: int = 32) -> list:
+	"""Splits `count` probes into power-of-two blocks (largest first), e.g. 200 -> 6x32 + 8."""
+	out, rest = [], int(count)
+	while rest > 0:
+		k = kmax
+		while k > rest:
+			k >>= 1
+		out.append(k)
+		rest -= k
+	return out
+
+
+class DeviceOperator:
+	"""A symmetric operator resident on the GPU (slq_op handle).
+
+	Accepts what the reference's FFI accepts (src/primate/_lanczos.cpp:104-111): a dense ndarray, a SciPy sparse
+	matrix/array (any format; converted to CSR once, not per call), or any object with `.matvec` and `.shape`
+	(slow host-callback path, include/pylinop.h:17-40).  The matrix is uploaded ONCE per operator.
+	"""
+
+	def __init__(self, A: Any, dtype=None):
+		import scipy.sparse as sp
+
+		torch = _torch()
+		L = _ffi.lib()
+		self.shape = tuple(A.shape)
+		assert len(self.shape) == 2 and self.shape[0] == self.shape[1], "This function only works with square, symmetric matrices!"
+		self.n = int(self.shape[0])
+		if dtype is None:
+			dtype = A.dtype if hasattr(A, "dtype") else np.float64
+		self.dtype = np.dtype(dtype)
+		self.code = _code(self.dtype)
+		self._keep = []
+		self._handle = ctypes.c_void_p()
+		self.h2d_bytes = 0
+		dev = torch.device("cuda", torch.cuda.current_device())
+		if sp.issparse(A):
+			C = A.tocsr()
+			C.sort_indices()
+			assert C.nnz < 2**31 - 1, "nnz must fit int32"
+			rowptr = torch.from_numpy(np.ascontiguousarray(C.indptr, dtype=np.int32)).to(dev, non_blocking=False)
+			colidx = torch.from_numpy(np.ascontiguousarray(C.indices, dtype=np.int32)).to(dev)
+			vals = torch.from_numpy(np.ascontiguousarray(C.data, dtype=self.dtype)).to(dev)
+			self._keep = [rowptr, colidx, vals]
+			self.h2d_bytes = rowptr.numel() * 4 + colidx.numel() * 4 + vals.numel() * vals.element_size()
+			self.kind, self.nnz = "csr", int(C.nnz)
+			_ffi.check(L.slq_csr_create(self.n, self.nnz, rowptr.data_ptr(), colidx.data_ptr(), vals.data_ptr(), self.code,
+			                            ctypes.byref(self._handle)))  # fmt: skip
+		elif isinstance(A, np.ndarray) or (hasattr(A, "is_cuda") and hasattr(A, "data_ptr")):
+			M = A if hasattr(A, "data_ptr") else torch.from_numpy(np.ascontiguousarray(A, dtype=self.dtype))
+			M = M.to(dev, dtype=_tdtype(self.dtype)).contiguous()
+			self._keep = [M]
+			self.h2d_bytes = M.numel() * M.element_size()
+			self.kind, self.nnz = "dense", self.n * self.n
+			_ffi.check(L.slq_dense_create(self.n, M.data_ptr(), self.n, self.code, ctypes.byref(self._handle)))
+		else:
+			if not hasattr(A, "matvec"):
+				raise ValueError("Supplied object is missing 'matvec' attribute.")  # pylinop.h:24
+			if not hasattr(A, "shape"):
+				raise ValueError("Supplied object is missing 'shape' attribute.")  # pylinop.h:25
+			self.kind, self.nnz = "callback", 0
+			self._A = A
+			self._cb = _ffi.MATMAT_FN(self._callback)
+			self._cb_error = None
+			_ffi.check(L.slq_callback_create(self.n, self.code, self._cb, None, ctypes.byref(self._handle)))
+		self._ws = {}
+
+	# host-callback operator: device panels out to the host, `A.matvec` per column, result back (pylinop.h:32-40)
+	def _callback(self, ctx, x_ptr, y_ptr, n, k, dtype, stream) -> int:
+		try:
+			torch = _torch()
+			ts = "<f8" if dtype == _ffi.SLQ_F64 else "<f4"
+			X = torch.as_tensor(_DevView(x_ptr, (n, k), ts), device="cuda")
+			Y = torch.as_tensor(_DevView(y_ptr, (n, k), ts), device="cuda")
+			if hasattr(self._A, "matmat_device"):  # GPU-native user operator: torch panels in, torch panels out
+				Y.copy_(self._A.matmat_device(X))
+				return 0
+			Xh = X.cpu().numpy()
+			Yh = np.empty_like(Xh)
+			for j in range(k):
+				Yh[:, j] = np.asarray(self._A.matvec(np.ascontiguousarray(Xh[:, j])), dtype=Xh.dtype).ravel()[:n]
+			Y.copy_(torch.from_numpy(Yh))
+			return 0
+		except Exception as exc:  # surfaced by the caller after the C call returns SLQ_ERR_CALLBACK
+			self._cb_error = exc
+			return 1
+
+	def __del__(self):
+		try:
+			if getattr(self, "_handle", None) is not None and self._handle.value:
+				_ffi.lib().slq_op_destroy(self._handle)
+				self._handle = ctypes.c_void_p()
+		except Exception:
+			pass
+
+	@property
+	def handle(self):
+		return self._handle
+
+	def workspace(self, k: int, ncv: int):
+		key = (k, ncv)
+		if key not in self._ws:
+			torch = _torch()
+			nbytes = _ffi.lib().slq_lanczos_workspace_bytes(self.n, k, ncv, self.code)
+			self._ws = {key: torch.empty(nbytes + 256, dtype=torch.uint8, device="cuda")}  # keep only the latest shape
+		buf = self._ws[key]
+		off = (-buf.data_ptr()) % 256
+		return buf.data_ptr() + off, buf.numel() - off
+
+	def _check(self, rc: int):
+		if rc == _ffi.SLQ_ERR_CALLBACK and getattr(self, "_cb_error", None) is not None:
+			exc, self._cb_error = self._cb_error, None
+			raise exc
+		_ffi.check(rc)
+
+	def matmat(self, X):
+		"""Y = A X for a device probe block X (n, k) row-major (torch tensor)."""
+		torch = _torch()
+		Y = torch.empty_like(X)
+		self._check(_ffi.lib().slq_op_matmat(self._handle, X.data_ptr(), Y.data_ptr(), int(X.shape[1]), _stream_ptr()))
+		return Y
+
+	def lanczos(self, X, deg: int, rtol: float = 1e-8, orth: int = 0, ncv: int = 2, want_basis: bool = False):
+		"""Blocked Lanczos on the device block X (n, k); X is clobbered.  Returns dict of device tensors."""
+		torch = _torch()
+		n, k = int(X.shape[0]), int(X.shape[1])
+		assert n == self.n and X.is_contiguous() and X.dtype == _tdtype(self.dtype)
+		alpha = torch.empty((k, deg + 1), dtype=X.dtype, device=X.device)
+		beta = torch.empty((k, deg + 1), dtype=X.dtype, device=X.device)
+		steps = torch.empty(k, dtype=torch.int32, device=X.device)
+		xnorm2 = torch.empty(k, dtype=torch.float64, device=X.device)
+		Q = torch.empty((ncv, n, k), dtype=X.dtype, device=X.device) if want_basis else None
+		ws_ptr, ws_bytes = self.workspace(k, ncv)
+		self._check(_ffi.lib().slq_lanczos(self._handle, X.data_ptr(), k, int(deg), float(rtol), int(orth), int(ncv), alpha.data_ptr(),
+		                                   beta.data_ptr(), steps.data_ptr(), xnorm2.data_ptr(), Q.data_ptr() if want_basis else None,
+		                                   ws_ptr, ws_bytes, _stream_ptr()))  # fmt: skip
+		return {"alpha": alpha, "beta": beta, "steps": steps, "xnorm2": xnorm2, "Q": Q}
+
+
+def fun_spec(fun, kwargs: Optional[dict] = None):
+	"""(fun_id, params) of a built-in spectral function name (special.py:78-107), or None for a Python callable."""
+	kw = dict(kwargs or {})
+	if fun is None or fun == "identity":
+		return 0, _ffi.fun_params()
+	if not isinstance(fun, str):
+		return None
+	if fun == "exp":
+		return 5, _ffi.fun_params(float(kw.get("t", 1.0)))
+	if fun == "smoothstep":
+		return 6, _ffi.fun_params(float(kw.get("a", 0.0)), float(kw.get("b", 1.0)))
+	if fun == "numrank":
+		return 7, _ffi.fun_params(float(kw.get("threshold", 0.000001)))
+	if fun == "softsign":
+		return 8, _ffi.fun_params(float(kw.get("q", 10)))
+	if fun in _ffi.FUN_IDS:
+		return _ffi.FUN_IDS[fun], _ffi.fun_params()
+	raise ValueError(f"Unknown function: {fun}.")
+
+
+def quadrature(alpha, beta, deg: int, fun_id: int = -1, params=None, scale=None, want_nodes: bool = True, want_y: bool = True):
+	"""Batched Golub-Welsch on device tensors alpha/beta (k, ld).  Returns (theta, tau, y, info) device tensors."""
+	torch = _torch()
+	k, ld = int(alpha.shape[0]), int(alpha.shape[1])
+	code = _ffi.SLQ_F64 if alpha.dtype == torch.float64 else _ffi.SLQ_F32
+	theta = torch.empty((k, deg), dtype=torch.float64, device=alpha.device) if want_nodes else None
+	tau = torch.empty((k, deg), dtype=torch.float64, device=alpha.device) if want_nodes else None
+	y = torch.empty(k, dtype=torch.float64, device=alpha.device) if (want_y and fun_id >= 0) else None
+	info = torch.empty(k, dtype=torch.int32, device=alpha.device)
+	_ffi.check(_ffi.lib().slq_quadrature(alpha.data_ptr(), beta.data_ptr(), code, k, int(deg), ld, int(fun_id),
+	                                     params if params is not None else _ffi.fun_params(),
+	                                     scale.data_ptr() if scale is not None else None,
+	                                     theta.data_ptr() if theta is not None else None, tau.data_ptr() if tau is not None else None,
+	                                     y.data_ptr() if y is not None else None, info.data_ptr(), _stream_ptr()))  # fmt: skip
+	return theta, tau, y, info
+
+
+def funm_coeffs(alpha, beta, deg: int, fun_id: int, params=None):
+	"""Krylov coefficients c_p = Y f(Theta) Y^T e_1 (k, deg) plus (theta, tau)."""
+	torch = _torch()
+	k, ld = int(alpha.shape[0]), int(alpha.shape[1])
+	code = _ffi.SLQ_F64 if alpha.dtype == torch.float64 else _ffi.SLQ_F32
+	kw = dict(dtype=torch.float64, device=alpha.device)
+	coeffs, theta, tau = torch.empty((k, deg), **kw), torch.empty((k, deg), **kw), torch.empty((k, deg), **kw)
+	scratch = torch.empty((k, deg, deg), **kw)
+	info = torch.empty(k, dtype=torch.int32, device=alpha.device)
+	_ffi.check(_ffi.lib().slq_funm_coeffs(alpha.data_ptr(), beta.data_ptr(), code, k, int(deg), ld, int(fun_id),
+	                                      params if params is not None else _ffi.fun_params(), coeffs.data_ptr(), theta.data_ptr(),
+	                                      tau.data_ptr(), scratch.data_ptr(), info.data_ptr(), _stream_ptr()))  # fmt: skip
+	return coeffs, theta, tau, scratch, info
+
+
+def rademacher_block(state: int, inc: int, first_probe: int, k: int, n: int, dtype):
+	"""Device Rademacher block (n, k) for probes first_probe .. first_probe+k-1 of the PCG64 stream (state, inc)."""
+	torch = _torch()
+	X = torch.empty((n, k), dtype=_tdtype(dtype), device="cuda")
+	_ffi.check(_ffi.lib().slq_probes_rademacher(_ffi.u128_pair(state), _ffi.u128_pair(inc), int(first_probe), int(k), int(n),
+	                                            _code(dtype), X.data_ptr(), _stream_ptr()))  # fmt: skip
+	return X
+
+
+def pcg64_raw(state: int, inc: int, offset: int, count: int):
+	torch = _torch()
+	out = torch.empty(count, dtype=torch.int64, device="cuda")
+	_ffi.check(_ffi.lib().slq_pcg64_raw(_ffi.u128_pair(state), _ffi.u128_pair(inc), int(offset), int(count), out.data_ptr(), _stream_ptr()))
+	return out.cpu().numpy().view(np.uint64)
+
+
+def block_from_columns(W: np.ndarray, dtype):
+	"""Uploads an (n, k) host panel (any order) and returns the device probe block (n, k) row-major."""
+	torch = _torch()
+	Wf = np.asfortranarray(W, dtype=np.dtype(dtype))
+	n, k = Wf.shape
+	cols = torch.from_numpy(Wf.T).to("cuda")  # (k, n) C-contiguous == F-ordered (n, k)
+	X = torch.empty((n, k), dtype=cols.dtype, device="cuda")
+	_ffi.check(_ffi.lib().slq_block_from_columns(cols.data_ptr(), n, k, _code(dtype), X.data_ptr(), _stream_ptr()))
+	return X
+
+
+def block_to_columns(X) -> np.ndarray:
+	"""Device probe block (n, k) -> host F-ordered (n, k) array."""
+	torch = _torch()
+	n, k = int(X.shape[0]), int(X.shape[1])
+	cols = torch.empty((k, n), dtype=X.dtype, device=X.device)
+	code = _ffi.SLQ_F64 if X.dtype == torch.float64 else _ffi.SLQ_F32
+	_ffi.check(_ffi.lib().slq_block_to_columns(X.data_ptr(), n, k, code, cols.data_ptr(), _stream_ptr()))
+	return cols.cpu().numpy().T
+
+
+def stats_update(y, state):
+	"""Chan merge of device samples y (m,) into device state (3,) = (count, mean, M2)."""
+	_ffi.check(_ffi.lib().slq_stats_update(y.data_ptr(), int(y.numel()), state.data_ptr(), _stream_ptr()))

@@ -1,0 +1,233 @@
+"""GPU parity of the C-ABI engine (libslq.so) against the golden vectors from the unmodified reference and
+against the CPU oracle on seeded inputs.  Bit-exact for probe signs / raw PCG64; 1e-10 rel for fp64 alpha/beta
+(north_star), 1e-4 for fp32; 1e-8 rel for quadrature values."""
+import numpy as np
+import pytest
+import scipy.sparse as sp
+
+from .conftest import laplacian_2d, rel_err
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def eng():
+	import torch
+
+	assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+	from primate_b200 import engine
+
+	return engine
+
+
+def _L30(golden):
+	return sp.csr_matrix((golden["L30_data"], golden["L30_indices"], golden["L30_indptr"]), shape=(900, 900))
+
+
+def _run_lanczos(eng, A, V, deg, orth=0, ncv=2, rtol=1e-8, dtype=np.float64, basis=False):
+	op = eng.DeviceOperator(A, dtype=dtype)
+	V = np.asarray(V, dtype=dtype)
+	V = V[:, None] if V.ndim == 1 else V
+	X = eng.block_from_columns(V, dtype)
+	out = op.lanczos(X, deg, rtol, orth, ncv, want_basis=basis)
+	res = {k: (v.cpu().numpy() if v is not None else None) for k, v in out.items()}
+	return res
+
+
+def test_device_is_blackwell(eng):
+	import ctypes
+
+	from primate_b200 import _ffi
+
+	sm, ma, mi = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+	_ffi.check(_ffi.lib().slq_device_info(ctypes.byref(sm), ctypes.byref(ma), ctypes.byref(mi)))
+	assert ma.value == 10 and sm.value > 0
+
+
+def test_pcg64_raw_bit_exact(eng, oracle, golden):
+	st, inc = oracle.pcg64_state(0)
+	assert np.array_equal(eng.pcg64_raw(st, inc, 0, 64), golden["raw_seed0_first64"])
+	bg = np.random.PCG64(0)
+	bg.advance(10**12 + 7)
+	assert np.array_equal(eng.pcg64_raw(st, inc, 10**12 + 7, 1000), bg.random_raw(1000))
+
+
+@pytest.mark.parametrize("seed,shape,key", [(123, (1000, 5), "signs_seed123_1000x5"), (99, (257, 33), "signs_seed99_257x33")])
+def test_rademacher_bit_exact_golden(eng, oracle, golden, seed, shape, key):
+	N, k = shape
+	st, inc = oracle.pcg64_state(seed)
+	G = golden[key].astype(np.float64) * 2 - 1
+	done = 0
+	for kb in eng.block_sizes(k, 32):
+		X = eng.rademacher_block(st, inc, done, kb, N, np.float64).cpu().numpy()
+		assert np.array_equal(X, G[:, done : done + kb])
+		done += kb
+	X32 = eng.rademacher_block(st, inc, 1, 4, N, np.float32).cpu().numpy()
+	assert X32.dtype == np.float32 and np.array_equal(X32, G[:, 1:5])
+
+
+def test_rademacher_large_offsets(eng, oracle):
+	"""probe index far into the stream (rank sharding): first_probe * n beyond 2^40."""
+	n, first = 100_003, 50_000_017
+	st, inc = oracle.pcg64_state(7)
+	X = eng.rademacher_block(st, inc, first, 2, n, np.float64).cpu().numpy()
+	for p in range(2):
+		ref = oracle.c_rademacher(st, inc, (first + p) * n, n)
+		assert np.array_equal(X[:, p], ref)
+
+
+@pytest.mark.parametrize("k", [1, 2, 4, 8, 16, 32, 64])
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+def test_spmm_vs_scipy(eng, k, dtype):
+	rng = np.random.default_rng(k)
+	A = laplacian_2d(37, dtype)
+	X = rng.standard_normal((A.shape[0], k)).astype(dtype)
+	op = eng.DeviceOperator(A, dtype=dtype)
+	Y = op.matmat(eng.block_from_columns(X, dtype)).cpu().numpy()
+	ref = A @ X
+	assert np.allclose(Y, ref, rtol=1e-13 if dtype == np.float64 else 1e-5, atol=1e-13 if dtype == np.float64 else 1e-5)
+
+
+def test_spmm_random_sparse_and_dense(eng):
+	rng = np.random.default_rng(3)
+	S = sp.random(501, 501, density=0.02, random_state=5, format="csr")
+	S = (S + S.T).tocsr()
+	X = rng.standard_normal((501, 8))
+	Y = eng.DeviceOperator(S).matmat(eng.block_from_columns(X, np.float64)).cpu().numpy()
+	assert np.allclose(Y, S @ X, rtol=1e-12, atol=1e-12)
+	D = rng.standard_normal((333, 333))
+	D = D + D.T
+	for k in (1, 4, 32):
+		Xk = rng.standard_normal((333, k))
+		Y = eng.DeviceOperator(D).matmat(eng.block_from_columns(Xk, np.float64)).cpu().numpy()
+		assert np.allclose(Y, D @ Xk, rtol=1e-11, atol=1e-11)
+
+
+@pytest.mark.parametrize("orth,ncv", [(0, 2), (0, 20), (3, 20), (20, 20), (5, 5)])
+def test_lanczos_dense_golden(eng, golden, orth, ncv):
+	A, v = golden["A150"], golden["v42"]
+	key = "lz_v42_deg20_orth5_nobasis" if (orth, ncv) == (5, 5) else f"lz_v42_deg20_orth{orth}"
+	res = _run_lanczos(eng, A, v, 20, orth=orth, ncv=ncv, basis=(ncv == 20))
+	assert rel_err(res["alpha"][0, :20], golden[key + "_a"]) < 1e-10
+	assert rel_err(res["beta"][0, 1:20], golden[key + "_b"]) < 1e-10
+	assert res["beta"][0, 0] == 0 and res["steps"][0] == 20 and abs(res["xnorm2"][0] - 150.0) < 1e-12
+	if ncv == 20:
+		Q = res["Q"][:, :, 0].T  # (n, ncv)
+		assert np.allclose(Q, golden[key + "_Q"], atol=1e-9)
+
+
+@pytest.mark.parametrize("orth", [0, 3])
+def test_lanczos_block_matches_per_probe_golden(eng, golden, orth):
+	"""a block of 4 probes == 4 independent reference runs (fresh basis per probe)."""
+	A, V = golden["A150"], golden["V4_seed7"]
+	res = _run_lanczos(eng, A, V, 20, orth=orth, ncv=20)
+	assert rel_err(res["alpha"][:, :20], golden[f"quad_log_orth{orth}_alpha"][:, :20]) < 1e-10
+	assert rel_err(res["beta"][:, 1:20], golden[f"quad_log_orth{orth}_beta"][:, 1:20]) < 1e-10
+
+
+@pytest.mark.parametrize("orth", [0, 3])
+def test_lanczos_sparse_golden(eng, golden, orth):
+	L, V = _L30(golden), golden["VL_seed0"]
+	Vp = np.concatenate([V, V[:, :1]], axis=1)  # pad to a power-of-two block
+	res = _run_lanczos(eng, L, Vp, 50, orth=orth, ncv=50)
+	assert rel_err(res["alpha"][:3, :50], golden[f"L30_quad_log_orth{orth}_alpha"][:, :50]) < 1e-10
+	assert rel_err(res["beta"][:3, 1:50], golden[f"L30_quad_log_orth{orth}_beta"][:, 1:50]) < 1e-10
+	assert np.array_equal(res["alpha"][3], res["alpha"][0])  # identical probes -> identical results (deterministic)
+
+
+def test_lanczos_fp32_golden(eng, golden):
+	L, V = _L30(golden), golden["VL_seed0"]
+	res = _run_lanczos(eng, L.astype(np.float32), V[:, 0], 50, dtype=np.float32)
+	assert res["alpha"].dtype == np.float32
+	assert rel_err(res["alpha"][0, :50], golden["L30_lz32_a"]) < 1e-4
+	assert rel_err(res["beta"][0, 1:50], golden["L30_lz32_b"]) < 1e-4
+	res = _run_lanczos(eng, golden["A150"].astype(np.float32), golden["v42"], 20, dtype=np.float32)
+	assert rel_err(res["alpha"][0, :20], golden["lz32_v42_deg20_a"]) < 1e-4
+	assert rel_err(res["beta"][0, 1:20], golden["lz32_v42_deg20_b"]) < 1e-4
+
+
+def test_lanczos_early_break_golden(eng, golden):
+	"""lanczos.h:140: rank-3 operator -> break after 3 steps, alpha/beta tails stay zero."""
+	B, V = golden["B60"], golden["VB_seed1"]
+	res = _run_lanczos(eng, B, V, 10)
+	for j in range(2):
+		ga, gb = golden[f"B60_lz_alpha_{j}"], golden[f"B60_lz_beta_{j}"]
+		assert res["steps"][j] == 3
+		assert np.allclose(res["alpha"][j, :3], ga[:3], rtol=1e-10) and np.allclose(res["beta"][j, 1:3], gb[1:3], rtol=1e-10)
+		assert np.all(res["alpha"][j, 3:] == 0) and np.all(res["beta"][j, 4:] == 0)
+		assert res["beta"][j, 3] < np.sqrt(60) * 1e-8
+
+
+def test_lanczos_vs_oracle_laplacian_blocks(eng, oracle):
+	"""seeded Rademacher block on a 2-D Laplacian, k=32 device block vs the compiled reference per probe."""
+	g = 64
+	A = laplacian_2d(g)
+	n = g * g
+	st, inc = oracle.pcg64_state(11)
+	X = eng.rademacher_block(st, inc, 0, 32, n, np.float64)
+	Xh = X.cpu().numpy().copy()
+	op = eng.DeviceOperator(A)
+	out = op.lanczos(X, 50, 1e-8, 0, 2)
+	al, be = out["alpha"].cpu().numpy(), out["beta"].cpu().numpy()
+	W = oracle.ref_isotropic((n, 32), "rademacher", 11)
+	assert np.array_equal(Xh, W)
+	for p in (0, 1, 15, 31):
+		ra, rb, _ = oracle.ref_lanczos(A, W[:, p], 50, 1e-8, 0)
+		assert rel_err(al[p, :50], ra[:50]) < 1e-10 and rel_err(be[p, 1:50], rb[1:50]) < 1e-10
+
+
+def test_quadrature_golden(eng, golden):
+	import torch
+
+	d, e = golden["T40_d"], golden["T40_e"]
+	for deg, kn, kw in ((40, "T40_gw_nodes", "T40_gw_weights"), (25, "T40_gw25_nodes", "T40_gw25_weights")):
+		a = torch.from_numpy(np.tile(d, (3, 1))).cuda()
+		b = torch.from_numpy(np.tile(e, (3, 1))).cuda()
+		theta, tau, y, info = eng.quadrature(a, b, deg, fun_id=0)
+		theta, tau = theta.cpu().numpy(), tau.cpu().numpy()
+		assert int(info.sum()) == 0
+		assert np.allclose(theta[1], golden[kn], rtol=0, atol=1e-13)
+		assert np.allclose(tau[1], golden[kw], rtol=0, atol=1e-12)
+		assert abs(y.cpu().numpy()[2] - np.sum(golden[kn] * golden[kw])) < 1e-12
+		assert abs(tau[0].sum() - 1.0) < 1e-13
+
+
+@pytest.mark.parametrize("fun,kw", [("identity", {}), ("abs", {}), ("sqrt", {}), ("log", {}), ("inv", {}),
+                                    ("exp", {"t": -0.5}), ("smoothstep", {"a": 0.2, "b": 0.6}),
+                                    ("numrank", {"threshold": 0.3})])  # fmt: skip
+@pytest.mark.parametrize("orth", [0, 3])
+def test_quad_builtins_golden(eng, golden, fun, kw, orth):
+	"""MatrixFunction.quad per probe (operators.py:126-151) == Lanczos block + fused quadrature."""
+	A, V = golden["A150"], golden["V4_seed7"]
+	op = eng.DeviceOperator(A)
+	out = op.lanczos(eng.block_from_columns(V, np.float64), 20, 1e-8, orth, 20)
+	fid, prm = eng.fun_spec(fun, kw)
+	theta, tau, y, info = eng.quadrature(out["alpha"], out["beta"], 20, fid, prm, scale=out["xnorm2"])
+	assert rel_err(y.cpu().numpy(), golden[f"quad_{fun}_orth{orth}"]) < 1e-8
+	if fun == "log":
+		assert np.allclose(theta.cpu().numpy(), golden[f"quad_log_orth{orth}_nodes"], atol=1e-11)
+		assert np.allclose(tau.cpu().numpy(), golden[f"quad_log_orth{orth}_weights"], atol=1e-11)
+
+
+def test_stats_update_matches_welford(eng, oracle):
+	import torch
+
+	rng = np.random.default_rng(0)
+	y = rng.standard_normal(200) * 1e3 - 1.3e7
+	w = oracle.Welford()
+	state = torch.zeros(3, dtype=torch.float64, device="cuda")
+	for lo in range(0, 200, 32):
+		chunk = y[lo : lo + 32]
+		w.update(chunk)
+		eng.stats_update(torch.from_numpy(chunk).cuda(), state)
+	s = state.cpu().numpy()
+	assert s[0] == 200 and abs(s[1] / w.mu - 1) < 1e-14 and abs(s[2] / w.S - 1) < 1e-12
+	assert abs(s[2] / 199 - np.var(y, ddof=1)) / np.var(y, ddof=1) < 1e-10
+
+
+def test_callback_operator(eng, golden):
+	from scipy.sparse.linalg import aslinearoperator
+
+	A, v = golden["A150"], golden["v42"]
+	res = _run_lanczos(eng, aslinearoperator(A), v, 20)
+	assert rel_err(res["alpha"][0, :20], golden["lz_v42_deg20_orth0_a"]) < 1e-10
