@@ -129,16 +129,19 @@ int slq_quadrature(const void* alpha_dev, const void* beta_dev, int dtype, int k
                    const double* params, const double* scale_dev, double* theta_dev, double* tau_dev,
                    double* y_dev, int32_t* info_dev, slq_stream stream);
 /* As slq_quadrature but also returns c_p = Y f(Theta) Y^T e_1 (k x deg doubles), the Krylov coefficients of
- * f(A)x (operators.py:122-124).  Needs deg*deg*k doubles of scratch. */
+ * f(A)x (operators.py:122-124).  scratch_dev: (deg*deg + deg)*k doubles; on return it holds, per matrix p, the
+ * eigenvector matrix Zt[p][col][row] (columns in QL order) followed at offset k*deg*deg by perm[p][i] = the Zt
+ * column of the i-th smallest Ritz value (so eigh_tridiag's Y[:, i] = Zt[p][perm[p][i]][:], tridiag.py:25-43). */
 int slq_funm_coeffs(const void* alpha_dev, const void* beta_dev, int dtype, int k, int deg, int ld, int fun,
                     const double* params, double* coeffs_dev, double* theta_dev, double* tau_dev,
                     double* scratch_dev, int32_t* info_dev, slq_stream stream);
 /* y[p] = scale[p] * sum_i f(theta[p][i]) * tau[p][i]   (fused evaluation on caller-provided nodes). */
 int slq_apply_fun(const double* theta_dev, const double* tau_dev, int k, int deg, int fun, const double* params,
                   const double* scale_dev, double* y_dev, slq_stream stream);
-/* FTTR weights (src/primate/fttr.py:5-29) for caller-provided nodes: theta k x deg -> tau k x deg. */
+/* FTTR weights (src/primate/fttr.py:5-29) for caller-provided nodes: theta k x deg -> tau k x deg, using the
+ * first `nterms` orthonormal polynomials of each Jacobi matrix (the reference's n = len(alpha)). */
 int slq_fttr(const double* theta_dev, const void* alpha_dev, const void* beta_dev, int dtype, int k, int deg,
-             int ld, double* tau_dev, slq_stream stream);
+             int nterms, int ld, double* tau_dev, slq_stream stream);
 
 /* ---- running statistics (src/primate/stats.py:66-86, estimators.py:128-141) ----------------------------- */
 /* Chan/Welford merge of a batch of m samples into state_dev = {count, mean, M2} (3 doubles, device). */

@@ -50,7 +50,7 @@ _SIGNATURES = {
 	"slq_funm_coeffs": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, POINTER(c_double), c_void_p, c_void_p,
 	                            c_void_p, c_void_p, c_void_p, c_void_p]),
 	"slq_apply_fun": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, POINTER(c_double), c_void_p, c_void_p, c_void_p]),
-	"slq_fttr": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
+	"slq_fttr": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
 	"slq_stats_update": (c_int, [c_void_p, c_int, c_void_p, c_void_p]),
 	"slq_basis_combine": (c_int, [c_void_p, c_int64, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
 }  # fmt: skip

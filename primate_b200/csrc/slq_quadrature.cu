@@ -184,6 +184,7 @@ __global__ void k_quadrature(const T* __restrict__ alpha, const T* __restrict__ 
     ts[rank] = ti;
     ws[rank] = z[i] * z[i];
     e[rank] = (double)i;  // e is free now: remember the permutation
+    if (Zscratch) Zscratch[(size_t)k * deg * deg + (size_t)p * deg + rank] = (double)i;  // sorted index -> Zt column
   }
   __syncwarp();
   const double sc = scale ? scale[p] : 1.0;
@@ -227,8 +228,8 @@ __global__ void k_apply_fun(const double* __restrict__ theta, const double* __re
 // FTTR weights (fttr.py:5-29): w_i = 1 / sum_j p_j(theta_i)^2 with the orthonormal polynomials of the Jacobi
 // matrix evaluated by the forward three-term recurrence, p_0 = 1/sqrt(mu_0), mu_0 = sum |theta|.  One thread per node.
 template <typename T>
-__global__ void k_fttr(const double* __restrict__ theta, const T* __restrict__ alpha, const T* __restrict__ beta, int k, int deg, int ld,
-                       double* __restrict__ tau) {
+__global__ void k_fttr(const double* __restrict__ theta, const T* __restrict__ alpha, const T* __restrict__ beta, int k, int deg,
+                       int nterms, int ld, double* __restrict__ tau) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int p = blockIdx.x * (blockDim.x >> 5) + warp;
   if (p >= k) return;
@@ -241,9 +242,9 @@ __global__ void k_fttr(const double* __restrict__ theta, const T* __restrict__ a
   for (int i = lane; i < deg; i += 32) {
     const double x = theta[(size_t)p * deg + i];
     double pm1 = mu_sqrt_rec;                                          // p_0
-    double pc = (deg > 1) ? (x - (double)a[0]) * pm1 / (double)b[1] : 0.0;  // p_1
-    double ss = pm1 * pm1 + ((deg > 1) ? pc * pc : 0.0);
-    for (int j = 2; j < deg; ++j) {
+    double pc = (nterms > 1) ? (x - (double)a[0]) * pm1 / (double)b[1] : 0.0;  // p_1
+    double ss = pm1 * pm1 + ((nterms > 1) ? pc * pc : 0.0);
+    for (int j = 2; j < nterms; ++j) {
       const double s = (x - (double)a[j - 1]) / (double)b[j];
       const double t = -(double)b[j - 1] / (double)b[j];
       const double pn = s * pc + t * pm1;
@@ -358,16 +359,16 @@ int slq_apply_fun(const double* theta_dev, const double* tau_dev, int k, int deg
   return SLQ_OK;
 }
 
-int slq_fttr(const double* theta_dev, const void* alpha_dev, const void* beta_dev, int dtype, int k, int deg, int ld, double* tau_dev,
-             slq_stream stream) {
+int slq_fttr(const double* theta_dev, const void* alpha_dev, const void* beta_dev, int dtype, int k, int deg, int nterms, int ld,
+             double* tau_dev, slq_stream stream) {
   SLQ_REQUIRE(theta_dev && alpha_dev && beta_dev && tau_dev, "NULL argument");
-  SLQ_REQUIRE(k > 0 && deg > 0 && ld >= deg, "invalid shape");
+  SLQ_REQUIRE(k > 0 && deg > 0 && nterms > 0 && ld >= nterms, "invalid shape");
   if (sm_count() <= 0) return fail(SLQ_ERR_CUDA, "no CUDA device");
   cudaStream_t st = (cudaStream_t)stream;
   if (dtype == SLQ_F64)
-    k_fttr<double><<<(unsigned)((k + 3) / 4), 128, 0, st>>>(theta_dev, (const double*)alpha_dev, (const double*)beta_dev, k, deg, ld, tau_dev);
+    k_fttr<double><<<(unsigned)((k + 3) / 4), 128, 0, st>>>(theta_dev, (const double*)alpha_dev, (const double*)beta_dev, k, deg, nterms, ld, tau_dev);
   else
-    k_fttr<float><<<(unsigned)((k + 3) / 4), 128, 0, st>>>(theta_dev, (const float*)alpha_dev, (const float*)beta_dev, k, deg, ld, tau_dev);
+    k_fttr<float><<<(unsigned)((k + 3) / 4), 128, 0, st>>>(theta_dev, (const float*)alpha_dev, (const float*)beta_dev, k, deg, nterms, ld, tau_dev);
   SLQ_LAUNCH_CHECK();
   return SLQ_OK;
 }

@@ -230,7 +230,7 @@ def funm_coeffs(alpha, beta, deg: int, fun_id: int, params=None):
 	code = _ffi.SLQ_F64 if alpha.dtype == torch.float64 else _ffi.SLQ_F32
 	kw = dict(dtype=torch.float64, device=alpha.device)
 	coeffs, theta, tau = torch.empty((k, deg), **kw), torch.empty((k, deg), **kw), torch.empty((k, deg), **kw)
-	scratch = torch.empty((k, deg, deg), **kw)
+	scratch = torch.empty(k * deg * deg + k * deg, **kw)
 	info = torch.empty(k, dtype=torch.int32, device=alpha.device)
 	_ffi.check(_ffi.lib().slq_funm_coeffs(alpha.data_ptr(), beta.data_ptr(), code, k, int(deg), ld, int(fun_id),
 	                                      params if params is not None else _ffi.fun_params(), coeffs.data_ptr(), theta.data_ptr(),
