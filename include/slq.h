@@ -68,6 +68,16 @@ const char* slq_last_error(void);
 /* SM count and compute capability of the current device (fails with SLQ_ERR_CUDA without one). */
 int slq_device_info(int* sm_count, int* cc_major, int* cc_minor);
 
+/* Number of CUDA kernels this library has launched in this process (bench.py's `gpu_launches`). */
+long long slq_launch_count(void);
+/* Optional timing of the library's own kernels with CUDA events on the launching stream, per kernel class:
+ * 0 = fused SpMM + recurrence kernel (Lanczos "step A"), 1 = axpy/norm/re-projection kernels, 2 = quadrature,
+ * 3 = probe generation.  enable(max) records at most `max` launches per class from now on (0 disables);
+ * read() synchronises on the recorded events and returns their summed duration, the number of launches timed and
+ * the number seen.  The reference has only dead `matvec_time` counters (include/eigen_operators.h:21,25,29). */
+int slq_profile_enable(int max_launches_per_class);
+int slq_profile_read(int kernel_class, double* total_ms, long long* timed_launches, long long* seen_launches);
+
 /* ---- operators (replace the per-call matrix wrappers: include/eigen_operators.h:18-104, _lanczos.cpp:93) - */
 /* CSR with int32 indices; arrays stay owned by the caller and must outlive the handle.  A must be symmetric
  * (as in the reference, which feeds the same symmetric matrix in CSC form). Column indices sorted per row is

@@ -30,6 +30,9 @@ _SIGNATURES = {
 	"slq_version": (c_int, []),
 	"slq_last_error": (c_char_p, []),
 	"slq_device_info": (c_int, [POINTER(c_int), POINTER(c_int), POINTER(c_int)]),
+	"slq_launch_count": (ctypes.c_longlong, []),
+	"slq_profile_enable": (c_int, [c_int]),
+	"slq_profile_read": (c_int, [c_int, POINTER(c_double), POINTER(ctypes.c_longlong), POINTER(ctypes.c_longlong)]),
 	"slq_csr_create": (c_int, [c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_int, POINTER(c_void_p)]),
 	"slq_dense_create": (c_int, [c_int64, c_void_p, c_int64, c_int, POINTER(c_void_p)]),
 	"slq_callback_create": (c_int, [c_int64, c_int, MATMAT_FN, c_void_p, POINTER(c_void_p)]),

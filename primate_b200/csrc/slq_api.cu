@@ -1,6 +1,9 @@
 // Library-level entry points of libslq: error reporting, device info, and the Krylov-basis combination used by
 // f(A) X (src/primate/operators.py:124: y = ||x|| * Q @ (Y (f(theta) o Y[0,:]))).
+#include <atomic>
 #include <cstring>
+#include <mutex>
+#include <vector>
 
 #include "slq_internal.cuh"
 
@@ -30,6 +33,44 @@ int sm_count() {
     cached = sms;
   }
   return cached;
+}
+
+static std::atomic<long long> g_launches{0};
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+
+// ---- event profiling (off by default) -----------------------------------------------------------------------
+struct ProfState {
+  std::mutex mu;
+  bool enabled = false;
+  int cap = 0;
+  std::vector<cudaEvent_t> ev[PROF_NCLASS];  // 2 events per slot
+  int used[PROF_NCLASS] = {0, 0, 0, 0};
+  long long seen[PROF_NCLASS] = {0, 0, 0, 0};
+};
+static ProfState g_prof;
+
+int prof_begin(int cls, cudaStream_t st) {
+  if (!g_prof.enabled) return -1;
+  std::lock_guard<std::mutex> lk(g_prof.mu);
+  g_prof.seen[cls]++;
+  if (g_prof.used[cls] >= g_prof.cap) return -1;
+  const int slot = g_prof.used[cls]++;
+  if ((int)g_prof.ev[cls].size() < 2 * (slot + 1)) {
+    cudaEvent_t a, b;
+    if (cudaEventCreate(&a) != cudaSuccess || cudaEventCreate(&b) != cudaSuccess) {
+      g_prof.used[cls]--;
+      return -1;
+    }
+    g_prof.ev[cls].push_back(a);
+    g_prof.ev[cls].push_back(b);
+  }
+  cudaEventRecord(g_prof.ev[cls][2 * slot], st);
+  return slot;
+}
+
+void prof_end(int cls, int slot, cudaStream_t st) {
+  if (slot < 0) return;
+  cudaEventRecord(g_prof.ev[cls][2 * slot + 1], st);
 }
 
 // Y[r][p] = sum_j Q[j][r][p] * (coef[p][j] * xnorm[p])
@@ -108,6 +149,32 @@ int slq_device_info(int* sm, int* cc_major, int* cc_minor) {
   if (sm) *sm = prop.multiProcessorCount;
   if (cc_major) *cc_major = prop.major;
   if (cc_minor) *cc_minor = prop.minor;
+  return SLQ_OK;
+}
+
+long long slq_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+int slq_profile_enable(int max_launches_per_class) {
+  std::lock_guard<std::mutex> lk(g_prof.mu);
+  g_prof.enabled = max_launches_per_class > 0;
+  g_prof.cap = max_launches_per_class > 0 ? max_launches_per_class : 0;
+  for (int c = 0; c < PROF_NCLASS; ++c) g_prof.used[c] = 0, g_prof.seen[c] = 0;
+  return SLQ_OK;
+}
+
+int slq_profile_read(int cls, double* total_ms, long long* timed_launches, long long* seen_launches) {
+  SLQ_REQUIRE(cls >= 0 && cls < PROF_NCLASS, "invalid profile class %d", cls);
+  std::lock_guard<std::mutex> lk(g_prof.mu);
+  double tot = 0.0;
+  for (int s = 0; s < g_prof.used[cls]; ++s) {
+    SLQ_CUDA(cudaEventSynchronize(g_prof.ev[cls][2 * s + 1]));
+    float ms = 0.f;
+    SLQ_CUDA(cudaEventElapsedTime(&ms, g_prof.ev[cls][2 * s], g_prof.ev[cls][2 * s + 1]));
+    tot += ms;
+  }
+  if (total_ms) *total_ms = tot;
+  if (timed_launches) *timed_launches = g_prof.used[cls];
+  if (seen_launches) *seen_launches = g_prof.seen[cls];
   return SLQ_OK;
 }
 

@@ -27,6 +27,7 @@ int fail(int code, const char* fmt, ...);
 
 #define SLQ_LAUNCH_CHECK()                                                                             \
   do {                                                                                                 \
+    ::slq::count_launch();                                                                             \
     cudaError_t _e = cudaGetLastError();                                                               \
     if (_e != cudaSuccess)                                                                             \
       return ::slq::fail(SLQ_ERR_CUDA, "kernel launch failed: %s (%s:%d)", cudaGetErrorString(_e), __FILE__, __LINE__); \
@@ -38,6 +39,13 @@ int fail(int code, const char* fmt, ...);
   } while (0)
 
 int sm_count();  // cached; <= 0 if no device
+void count_launch();  // host-side counter of kernels launched by the library (slq_launch_count)
+
+// Optional per-kernel-class timing with CUDA events on the launching stream (slq_profile_*): used by bench.py to
+// get the dominant kernel's average launch duration inside the timed region.  No-ops unless enabled.
+enum ProfClass { PROF_STEPA = 0, PROF_AXPY = 1, PROF_QUAD = 2, PROF_PROBES = 3, PROF_NCLASS = 4 };
+int prof_begin(int cls, cudaStream_t st);             // returns a slot (>= 0) or -1 when not recording
+void prof_end(int cls, int slot, cudaStream_t st);
 
 inline bool is_pow2(int k) { return k > 0 && (k & (k - 1)) == 0; }
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }

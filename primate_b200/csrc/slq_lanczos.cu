@@ -543,6 +543,7 @@ static int lanczos_impl(slq_op* op, T* X, int deg, double rtol, int orth, int nc
     const bool first = (pp < 0);
     const T* upp = first ? phys[pc] : phys[pp];
     const double* scp = first ? scale_of(pc) : scale_of(pp);
+    const int pslot = prof_begin(PROF_STEPA, st);
     if (op->kind == OP_CSR) {
       if (first)
         k_stepA<T, K, true, true><<<g_row, NT, 0, st>>>(n, op->rowptr, op->colidx, (const T*)op->vals, phys[pc], upp, w, ws.sc,
@@ -561,6 +562,7 @@ static int lanczos_impl(slq_op* op, T* X, int deg, double rtol, int orth, int nc
                                                           ws.partial, so);
     }
     SLQ_LAUNCH_CHECK();
+    prof_end(PROF_STEPA, pslot, st);
 
     // columns visited by the re-projection: c, c-1, ... cyclically, `orth` of them; unwritten (zero) columns are
     // skipped exactly as the reference's u_norm > tol guard skips them (lanczos.h:58-64, fresh basis).
@@ -568,8 +570,10 @@ static int lanczos_impl(slq_op* op, T* X, int deg, double rtol, int orth, int nc
     for (int t = 0, i = c; t < orth; ++t, i = ((i - 1) % ncv + ncv) % ncv)
       if (slot_phys[i] >= 0) visit.push_back(slot_phys[i]);
     if (visit.empty()) {
+      const int bslot = prof_begin(PROF_AXPY, st);
       k_axpy<T, K, AX_NORM><<<g_vec, NT, 0, st>>>(n, w, phys[pc], nullptr, ws.sc, scale_of(F), nullptr, ws.partial, so);
       SLQ_LAUNCH_CHECK();
+      prof_end(PROF_AXPY, bslot, st);
     } else {
       // visit[0] is always the current column: fuse "v = w - alpha q_c" with the first projection's dots
       k_axpy<T, K, AX_DOT_SAME><<<g_vec, NT, 0, st>>>(n, w, phys[pc], nullptr, ws.sc, nullptr, scale_of(visit[0]), ws.partial, so);

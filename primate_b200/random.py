@@ -99,6 +99,8 @@ class ProbeStream:
 			X = engine.rademacher_block(self._state, self._inc, first, k, self.n, self.dtype)
 			self.position = max(self.position, first + k)
 			return X
+		if first is not None and first > self.position:
+			self.skip(first - self.position)  # another rank's probes: drawn and dropped to stay on the one stream
 		assert first is None or first == self.position, "host-generated probe streams are sequential"
 		W = np.empty((self.n, k), dtype=np.float64, order="F")
 		_ISO_FUNCS[self.pdf](self.rng, W)

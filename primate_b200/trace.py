@@ -1,0 +1,353 @@
+"""Trace estimators (API mirror of src/primate/trace.py:34-315) driven by the device engine.
+
+`hutch` keeps the reference's signature, defaults, stopping cadence and results, but the Monte-Carlo loop
+(trace.py:107-116: draw one probe -> `A.quad(v)` -> `estimator.update` -> `converge(estimator)`) runs on blocks of
+up to 32 probes generated IN GPU memory (bit-identical to `isotropic(pdf, seed)` drawn column by column), pushed
+through the probe-blocked Lanczos + Golub-Welsch kernels, and only the per-probe quadrature values (k doubles per
+block, or a 3-double (count, mean, M2) record per rank) come back.  The host then replays the reference's update /
+check sequence on those scalars, so the estimate, the number of samples consumed and the final state of a
+user-supplied Generator are the reference's.  With torch.distributed initialised (one process per GPU) the probes
+are sharded over the ranks (primate_b200.sharding).
+"""
+from typing import Callable, Optional, Union
+
+import numpy as np
+from scipy.sparse.linalg import LinearOperator
+
+from . import engine, sharding
+from .estimators import (
+	ConfidenceCriterion,
+	ConvergenceCriterion,
+	CountCriterion,
+	EstimatorResult,
+	MeanEstimator,
+	convergence_criterion,
+)
+from .linalg import update_trinv
+from .operators import MatrixFunction, is_valid_operator
+from .random import ProbeStream, isotropic
+
+KMAX = 32  # probes per device block (power of two <= 64)
+
+
+# ---- Monte-Carlo driver shared by the device paths (and by the CPU gloo tests, with an injected sampler) --------
+def _to_host(y) -> np.ndarray:
+	return y.detach().cpu().numpy().ravel() if hasattr(y, "detach") else np.asarray(y, dtype=np.float64).ravel()
+
+
+def _concat(parts: list):
+	if len(parts) == 1:
+		return parts[0]
+	if hasattr(parts[0], "detach"):
+		import torch
+
+		return torch.cat(parts)
+	return np.concatenate(parts)
+
+
+def _sample_range(sample_block: Callable, lo: int, hi: int, kmax: int):
+	"""Quadrature samples of probes [lo, hi) as one (hi-lo,) array, computed in power-of-two blocks."""
+	parts, first = [], lo
+	for k in engine.block_sizes(hi - lo, kmax):
+		parts.append(sample_block(first, k))
+		first += k
+	return _concat(parts) if parts else np.zeros(0)
+
+
+def _pad(y, m: int):
+	"""Pads a (<= m,) sample vector to length m with NaN so that every rank contributes the same size."""
+	have = int(y.shape[0])
+	if have == m:
+		return y
+	if hasattr(y, "detach"):
+		import torch
+
+		return torch.cat([y, torch.full((m - have,), float("nan"), dtype=y.dtype, device=y.device)])
+	return np.concatenate([np.asarray(y, dtype=np.float64), np.full(m - have, np.nan)])
+
+
+def _run_fixed_count(sample_block, estimator, total: int, comm, kmax: int, stats_fn=None) -> int:
+	"""`CountCriterion` with per-probe cadence: exactly `total` more probes; one collective at the end."""
+	if total <= 0:
+		return 0
+	lo, hi = sharding.probe_range(total, comm.rank, comm.size)
+	y = _sample_range(sample_block, lo, hi, kmax)
+	if comm.size > 1 and estimator.values is None and stats_fn is not None:
+		# (count, mean, M2) per rank, reduced on the device; ONE all-gather of 3 doubles per rank
+		rec = stats_fn(y) if hi > lo else np.zeros(3)
+		for cnt, mean, m2 in comm.all_gather(rec):
+			estimator.merge(int(cnt), mean, m2)
+		return total
+	per = -(-total // comm.size)
+	allv = comm.all_gather(_pad(y, per)).ravel() if comm.size > 1 else _to_host(y)
+	allv = allv[~np.isnan(allv)] if comm.size > 1 else allv
+	assert allv.size == total
+	if total > 1:
+		estimator.update(allv[:-1])
+	estimator.update(allv[-1:])  # the reference's last update is a single sample: keeps `estimator.delta` meaningful
+	return total
+
+
+def _run_per_probe(sample_block, estimator, converge, comm, kmax: int) -> int:
+	"""Adaptive criterion, per-probe cadence (trace.py:114-116): speculate one block per rank, replay on the host."""
+	consumed = 0
+	while not converge(estimator):
+		first, k = sharding.round_blocks(consumed, kmax, comm.rank, comm.size)
+		vals = comm.all_gather(sample_block(first, k)).ravel()  # global probe order: rank-major == index order
+		for v in vals:
+			estimator.update(v)
+			consumed += 1
+			if converge(estimator):
+				break
+	return consumed
+
+
+def _run_batched(sample_block, estimator, converge, batch: int, callback, result, comm, kmax: int) -> int:
+	"""`full=True` / callback cadence (trace.py:107-110): `batch` probes per update, one check per batch."""
+	consumed = 0
+	while not converge(estimator):
+		lo, hi = sharding.probe_range(batch, comm.rank, comm.size)
+		y = _sample_range(sample_block, consumed + lo, consumed + hi, kmax)
+		if comm.size > 1:
+			per = -(-batch // comm.size)
+			vals = comm.all_gather(_pad(y, per)).ravel()
+			vals = vals[~np.isnan(vals)]
+		else:
+			vals = _to_host(y)
+		estimator.update(vals)
+		consumed += batch
+		callback(result)
+	return consumed
+
+
+def _device_sampler(A, stream: ProbeStream):
+	"""probe range -> device quadrature samples for a MatrixFunction (SLQ) or an explicit matrix (x^T A x)."""
+	if isinstance(A, MatrixFunction):
+		return lambda first, k: A.quad_block(stream.block(k, first))
+	from .lanczos import device_operator
+
+	dev = device_operator(A, stream.dtype)
+
+	def _quad(first: int, k: int):
+		import torch
+
+		X = stream.block(k, first)
+		Y = dev.matmat(X)
+		return (X.to(torch.float64) * Y.to(torch.float64)).sum(dim=0)
+
+	return _quad
+
+
+def _device_stats(y):
+	"""(count, mean, M2) of device samples, reduced by libslq (slq_stats_update); 3 doubles stay on the device."""
+	import torch
+
+	state = torch.zeros(3, dtype=torch.float64, device=y.device)
+	engine.stats_update(y.contiguous(), state)
+	return state
+
+
+def _on_device(A) -> bool:
+	import scipy.sparse as sp
+
+	return isinstance(A, MatrixFunction) or isinstance(A, np.ndarray) or sp.issparse(A)
+
+
+def hutch(
+	A: Union[LinearOperator, np.ndarray],
+	batch: int = 32,
+	pdf: Union[str, Callable] = "rademacher",
+	converge: Union[str, ConvergenceCriterion] = "default",
+	seed: Union[int, np.random.Generator, None] = None,
+	full: bool = False,
+	callback: Optional[Callable] = None,
+	**kwargs,
+) -> Union[float, tuple]:
+	r"""Estimates the trace of a symmetric `A` (or of `f(A)` for a `MatrixFunction`) with the Girard-Hutchinson estimator.
+
+	Parameters are the reference's (trace.py:34-43): `batch` probes per update when `full`/`callback` is used (one
+	probe per update otherwise), `pdf` the isotropic distribution (or a sampler callable), `converge` a criterion name
+	or object ("default" = 200 samples OR a 95% CLT margin below 1.0), `seed` an int or Generator, remaining keyword
+	arguments parameterise the criterion.  Extra keyword (not in the reference): `comm` -- "auto" (default) shards the
+	probes over the ranks of an initialised torch.distributed group, `None` keeps everything on this process.
+	"""
+	f_dtype = is_valid_operator(A)
+	N: int = A.shape[0]
+	comm = sharding.resolve_comm(kwargs.pop("comm", "auto"))
+
+	rng = np.random.default_rng(seed)
+	estimator = MeanEstimator(covariance=True, record=kwargs.pop("record", False))
+	if converge == "default":
+		converge = CountCriterion(count=200) | ConfidenceCriterion(confidence=0.95, atol=1.0, rtol=0.0)
+	else:
+		converge = convergence_criterion(converge, **kwargs)
+
+	if np.prod(A.shape) == 0:
+		return 0.0 if not full else (0.0, EstimatorResult(estimator, converge))
+
+	batched = full or callback is not None
+	result = EstimatorResult(estimator, converge)
+	cb = (lambda x: x) if callback is None else callback
+
+	if isinstance(pdf, str) and _on_device(A):
+		stream = ProbeStream(N, pdf, seed=rng, dtype=f_dtype)
+		sampler = _device_sampler(A, stream)
+		if batched:
+			consumed = _run_batched(sampler, estimator, converge, int(batch), cb, result, comm, KMAX)
+		elif type(converge) is CountCriterion:
+			consumed = _run_fixed_count(sampler, estimator, converge.count - len(estimator), comm, KMAX, _device_stats)
+		else:
+			consumed = _run_per_probe(sampler, estimator, converge, comm, KMAX)
+		stream.finish(consumed)
+	else:
+		# host operators / user samplers: the reference's loop, one host probe (or batch) at a time
+		draw = isotropic(pdf=pdf, seed=rng) if isinstance(pdf, str) else pdf
+		quad_form = (lambda v: A.quad(v)) if hasattr(A, "quad") else (lambda v: np.einsum("...i,...i->...", v.T, (A @ v).T))
+		while not converge(estimator):
+			v = draw(size=(N, batch if batched else 1)).astype(f_dtype)
+			estimator.update(quad_form(v))
+			if batched:
+				cb(result)
+	if batched:
+		result.message = converge.message(estimator)
+		result.estimate = estimator.estimate
+		result.nit = len(estimator)
+		return (estimator.estimate, result)
+	return estimator.estimate
+
+
+def _quad_columns(A, Q: np.ndarray) -> np.ndarray:
+	"""q^T A q for every column of Q (one blocked device call for a MatrixFunction)."""
+	if hasattr(A, "quad"):
+		return np.ravel(A.quad(Q))
+	return np.einsum("ij,ij->j", Q, A @ Q)
+
+
+def hutchpp(
+	A: Union[LinearOperator, np.ndarray],
+	m: Optional[int] = None,
+	batch: int = 32,
+	mode: str = "reduced",
+	pdf: Union[str, Callable] = "rademacher",
+	seed: Union[int, np.random.Generator, None] = None,
+	full: bool = False,
+) -> Union[float, dict]:
+	"""Hutch++ estimator (trace.py:119-182): exact trace on a sketched range + Hutchinson on the deflated remainder.
+
+	`m` probes go to each of the two phases (default n // 3, bumped by `m % 3` as in the reference); `batch` is
+	unused.  All products with `A` are block products (`A @ block`), i.e. blocked device Lanczos for a MatrixFunction.
+	"""
+	f_dtype = is_valid_operator(A)
+	N: int = A.shape[0]
+	rng = np.random.default_rng(seed)
+	draw = isotropic(pdf=pdf, seed=rng)
+	if np.prod(A.shape) == 0:
+		return 0.0 if not full else (0.0, EstimatorResult())
+
+	nb = (N // 3) if m is None else m
+	nb += nb % 3
+
+	## range sketch
+	WB = draw(size=(N, nb)).astype(f_dtype)
+	Q = np.linalg.qr(A @ WB, mode="reduced")[0]
+	rng_ests = np.einsum("ij,ij->j", A @ Q, Q) if mode == "full" else _quad_columns(A, Q)
+	tr_rng = np.sum(rng_ests)
+
+	## Hutchinson on the complement of range(Q)
+	G = draw(size=(N, nb)).astype(f_dtype)
+	G -= Q @ (Q.T @ G)
+	defl_ests = np.einsum("ij,ij->j", A @ G, G)
+	tr_defl = np.sum(defl_ests) / nb
+
+	if not full:
+		return tr_rng + tr_defl
+	result = EstimatorResult()
+	result.estimate = tr_rng + tr_defl
+	result.nit = 2 * nb
+	result.samples = np.concatenate([np.ravel(rng_ests), defl_ests])
+	return result.estimate, result
+
+
+def _xtrace(W: np.ndarray, Z: np.ndarray, Q: np.ndarray, R: np.ndarray, R_inv: np.ndarray, pdf: str):
+	"""Leave-one-out XTrace samples (trace.py:185-227) from the probes W, Q/R of qr(A W), Z = A Q and R^{-1}."""
+
+	def dprod(X, Y):  # diag(X^T Y) as a column
+		return np.einsum("ij,ij->j", X, Y)[:, np.newaxis]
+
+	n, m = W.shape
+	QtW = Q.T @ W
+	S = R_inv.T / np.linalg.norm(R_inv, axis=1)  # unit-norm columns spanning the leave-one-out directions
+
+	if not pdf == "sphere":
+		scale = np.ones((m, 1))
+	else:
+		cn = lambda X: np.linalg.norm(X, axis=0)  # noqa: E731
+		scale = (n - m + 1) / (n - (cn(QtW)[:, np.newaxis]) ** 2 + (dprod(S, QtW) * cn(S)[:, np.newaxis]) ** 2)
+
+	H = Q.T @ Z
+	HW = H @ QtW
+	T = Z.T @ W
+	dSW, dSHS = dprod(S, QtW), dprod(S, H @ S)
+	dTW, dWHW = dprod(T, QtW), dprod(QtW, HW)
+	dSRmHW, dTmHRS = dprod(S, R - HW), dprod(T - H.T @ QtW, S)
+
+	ests = np.trace(H) * np.ones((m, 1)) - dSHS
+	ests += (-dTW + dWHW + dSW * dSRmHW + abs(dSW) ** 2 * dSHS + dTmHRS * dSW) * scale
+	return ests
+
+
+def xtrace(
+	A: Union[LinearOperator, np.ndarray],
+	batch: int = 32,
+	pdf: Union[str, Callable] = "sphere",
+	converge: Union[str, ConvergenceCriterion] = "default",
+	seed: Union[int, np.random.Generator, None] = None,
+	full: bool = False,
+	callback: Optional[Callable] = None,
+	**kwargs,
+) -> Union[float, tuple]:
+	"""Epperly's exchangeable XTrace estimator (trace.py:233-315): grows a sketch batch by batch and averages the
+	leave-one-out estimates.  Signature and quirks are the reference's (a `CountCriterion(n)` is always in force and a
+	user `converge` is OR-ed onto it; the probes' `pdf` reaches `_xtrace` as a sampler, so no sphere rescaling)."""
+	from scipy.linalg import qr_insert
+
+	assert batch >= 1, "Batch size must be positive."
+	n = A.shape[0]
+	callback = (lambda result: ...) if not callable(callback) else callback
+	record = kwargs.pop("record", False)
+	estimator = MeanEstimator(record=record)
+
+	if converge == "default":
+		converge = CountCriterion(count=n)
+	else:
+		converge = CountCriterion(count=n)
+		converge |= convergence_criterion(converge, **kwargs)
+	assert isinstance(converge, ConvergenceCriterion)
+
+	W = np.zeros(shape=(n, 0), order="F")
+	Y = np.zeros(shape=(n, 0))
+	Z = np.zeros(shape=(n, 0), order="F")
+	Q, R = np.linalg.qr(Y, mode="reduced")
+	R_inv = np.zeros(shape=(0, 0))
+
+	result = EstimatorResult()
+	rng = np.random.default_rng(seed)
+	pdf = isotropic(pdf=pdf, seed=rng) if isinstance(pdf, str) else pdf
+	while not converge(estimator):
+		ns = min(A.shape[1] - W.shape[1], int(batch))
+		Nw = pdf(size=(n, ns))
+		Y = A @ Nw
+		for j in range(ns):
+			Q, R = qr_insert(Q, R, u=Y[:, j], k=Q.shape[1], which="col")
+			R_inv = update_trinv(R_inv, R[:, -1])
+		W = np.c_[W, Nw]
+		Z = np.c_[Z, A @ Q[:, -ns:]]
+		t_samples = _xtrace(W, Z, Q, R, R_inv, pdf)
+		estimator = MeanEstimator(record=record)
+		estimator.update(t_samples.ravel())
+		callback(result)
+
+	result.estimator = estimator
+	result.estimate = estimator.estimate
+	result.criterion = converge
+	return (result.estimate, result) if full else result.estimate

@@ -1,0 +1,170 @@
+"""GPU parity of the reference-facing Python API (primate_b200.{lanczos,operators,trace,diagonal}) against golden
+vectors produced by the unmodified reference, and -- at BASELINE.json's full C2 size -- against the oracle on sampled
+probe indices plus size-independent properties.  Tolerances: alpha/beta 1e-10 rel (fp64), estimates 1e-8 rel."""
+import numpy as np
+import pytest
+import scipy.sparse as sp
+
+from .conftest import laplacian_2d, rel_err
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _cuda():
+	import torch
+
+	assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+
+
+def _L30(golden):
+	return sp.csr_matrix((golden["L30_data"], golden["L30_indices"], golden["L30_indptr"]), shape=(900, 900))
+
+
+def test_lanczos_api_golden(golden):
+	from primate_b200.lanczos import lanczos
+
+	A = golden["A150"]
+	a, b = lanczos(A, deg=10, seed=0, orth=0)
+	assert rel_err(a, golden["lz_seed0_deg10_a"]) < 1e-10 and rel_err(b, golden["lz_seed0_deg10_b"]) < 1e-10
+	for orth in (0, 3, 20):
+		(a, b), Q = lanczos(A, v0=golden["v42"], deg=20, orth=orth, return_basis=True)
+		assert rel_err(a, golden[f"lz_v42_deg20_orth{orth}_a"]) < 1e-10
+		assert rel_err(b, golden[f"lz_v42_deg20_orth{orth}_b"]) < 1e-10
+		assert Q.shape == (150, 20) and Q.flags["F_CONTIGUOUS"]
+		assert np.max(np.abs(Q - golden[f"lz_v42_deg20_orth{orth}_Q"])) < 1e-9
+	a, b = lanczos(A, v0=golden["v42"], deg=20, orth=5)
+	assert rel_err(a, golden["lz_v42_deg20_orth5_nobasis_a"]) < 1e-10
+	T = lanczos(A, v0=golden["v42"], deg=20, orth=0, sparse_mat=True)
+	assert T.shape == (20, 20) and rel_err(T.diagonal(), golden["lz_v42_deg20_orth0_a"]) < 1e-10
+
+
+def test_hutch_goldens_and_generator_state(golden):
+	from primate_b200.operators import MatrixFunction
+	from primate_b200.trace import hutch
+
+	A = golden["A150"]
+	M = MatrixFunction(A, "log", deg=20, orth=0)
+	rng = np.random.default_rng(5)
+	est = hutch(M, converge="count", count=200, seed=rng)
+	assert abs(est / golden["hutch_log_count200_seed5"].item() - 1) < 1e-8
+	# the user's Generator is left where the reference leaves it: 200 probes x 150 raw draws
+	chk = np.random.default_rng(5)
+	chk.bit_generator.advance(200 * 150)
+	assert rng.bit_generator.state["state"] == chk.bit_generator.state["state"]
+
+	est, res = hutch(M, converge="count", count=200, seed=5, full=True, batch=32, record=True)
+	assert abs(est / golden["hutch_log_count200_seed5_full_b32"].item() - 1) < 1e-8
+	assert len(res.estimator) == 224
+	assert rel_err(np.ravel(res.estimator.values), golden["hutch_log_count200_seed5_full_b32_samples"]) < 1e-8
+
+	est, res = hutch(M, seed=11, full=True, batch=1, record=True)
+	assert len(res.estimator) == int(golden["hutch_log_default_seed11_n"])
+	assert abs(est / golden["hutch_log_default_seed11"].item() - 1) < 1e-8
+	est = hutch(M, seed=11)  # per-probe cadence on speculative blocks stops at the same probe
+	assert abs(est / golden["hutch_log_default_seed11"].item() - 1) < 1e-8
+
+	est, res = hutch(M, converge="confidence", confidence=0.9, atol=2.0, rtol=0.0, seed=3, full=True, batch=8, record=True)
+	assert len(res.estimator) == int(golden["hutch_log_conf_seed3_b8_n"])
+	assert abs(est / golden["hutch_log_conf_seed3_b8"].item() - 1) < 1e-8
+
+	assert abs(hutch(A, seed=2) / golden["hutch_A_default_seed2"].item() - 1) < 1e-8  # plain matrix: x^T A x on the device
+	M3 = MatrixFunction(A, "exp", deg=12, orth=0, t=0.25)
+	assert abs(hutch(M3, converge="count", count=64, seed=9) / golden["hutch_exp_count64_seed9"].item() - 1) < 1e-8
+	ML = MatrixFunction(_L30(golden), "log", deg=50, orth=0)
+	assert abs(hutch(ML, converge="count", count=64, seed=0) / golden["L30_hutch_log_count64_seed0"].item() - 1) < 1e-8
+
+
+def test_hutch_host_callable_fun_and_normal_pdf(golden, oracle):
+	"""User callables are evaluated on the host on the (k x deg) Ritz values; normal probes come from the host stream."""
+	from primate_b200.operators import MatrixFunction
+	from primate_b200.trace import hutch
+
+	A = golden["A150"]
+	M = MatrixFunction(A, fun=lambda x: np.log(np.maximum(x, np.finfo(float).eps)), deg=20, orth=0)
+	assert abs(hutch(M, converge="count", count=200, seed=5) / golden["hutch_log_count200_seed5"].item() - 1) < 1e-8
+	Mn = MatrixFunction(A, "log", deg=20, orth=0)
+	est = hutch(Mn, pdf="normal", converge="count", count=40, seed=21)
+	W = np.empty((150, 40), order="F")
+	np.random.default_rng(21).standard_normal(out=W)
+	ref = oracle.ref_quad(A, W, "log", deg=20, orth=0).mean()
+	assert abs(est / ref - 1) < 1e-8
+
+
+def test_matrix_function_matvec_goldens(golden):
+	from primate_b200.operators import MatrixFunction
+
+	A, v = golden["A150"], golden["v42"]
+	for fun, kw in (("log", {}), ("exp", {"t": -0.5}), ("identity", {})):
+		for orth in (0, 20):
+			M = MatrixFunction(A, fun, deg=20, orth=orth, **kw)
+			y = np.ravel(M._matvec(v.copy()))
+			g = golden[f"matvec_{fun}_orth{orth}_v42"]
+			assert np.max(np.abs(y - g)) < 1e-8 * np.max(np.abs(g)), (fun, orth)
+	M = MatrixFunction(A, "identity", deg=150, orth=150)
+	V = np.random.default_rng(0).standard_normal((150, 5))
+	assert np.allclose(M @ V, A @ V, atol=1e-8)  # SciPy LinearOperator interface
+	assert np.allclose(M.quad(V), np.einsum("ij,ij->j", V, A @ V), rtol=1e-9)  # tests/test_operator.py:35-46
+
+
+def test_block_drivers_on_matrix_function(golden):
+	"""hutch++ / xdiag with a MatrixFunction: every `A @ block` is blocked device Lanczos (tests/test_trace.py:36-45)."""
+	from primate_b200.diagonal import xdiag
+	from primate_b200.operators import MatrixFunction
+	from primate_b200.trace import hutchpp
+
+	A = golden["A150"]
+	ew, U = np.linalg.eigh(A)
+	expA = (U * np.exp(0.5 * ew)) @ U.T
+	M = MatrixFunction(A, "exp", deg=40, orth=40, t=0.5)
+	assert abs(hutchpp(M, m=60, seed=1) - np.trace(expA)) < 1e-2 * np.trace(expA)
+	d = xdiag(M, m=120, seed=2, pdf="rademacher")
+	assert np.linalg.norm(d - np.diag(expA)) < 0.1 * np.linalg.norm(np.diag(expA))
+
+
+@pytest.fixture(scope="module")
+def c2():
+	A = laplacian_2d(1000)
+	return A
+
+
+def test_c2_full_size_parity_on_sampled_probes(c2, oracle):
+	"""n = 1e6, deg = 50: alpha/beta of probes at block and rank edges vs the reference extension (1e-10), their
+	quadrature values (1e-8), and bit-exact signs."""
+	from primate_b200 import engine
+	from primate_b200.operators import MatrixFunction
+
+	n, deg = c2.shape[0], 50
+	st, inc = oracle.pcg64_state(0)
+	M = MatrixFunction(c2, "log", deg=deg, orth=0)
+	for first in (0, 4992, 9984):  # blocks holding probes 0, 31 | 4999 | 9999
+		X = engine.rademacher_block(st, inc, first, 32, n, np.float64)
+		Xh = X.cpu().numpy()
+		y, out = M.quad_block(X, keep_tridiag=True)
+		y, al, be = y.cpu().numpy(), out["alpha"].cpu().numpy(), out["beta"].cpu().numpy()
+		for p in {0: (0, 31), 4992: (7,), 9984: (15,)}[first]:
+			sign = oracle.c_rademacher(st, inc, (first + p) * n, n)
+			assert np.array_equal(Xh[:, p], sign)
+			ra, rb = oracle.ref_lanczos(c2, sign.copy(), deg, 1e-8, 0, ncv=2)[:2]
+			assert rel_err(al[p, :deg], ra[:deg]) < 1e-10 and rel_err(be[p, 1:deg], rb[1:deg]) < 1e-10
+			ry = oracle.ref_quad(c2, sign, "log", deg=deg, orth=0)[0]
+			assert abs(y[p] / ry - 1) < 1e-8
+
+
+def test_c2_full_size_properties(c2):
+	"""Size-independent checks at n = 1e6: quad is invariant to the block a probe travels in and to its slot; tr(A) by
+	identity-f hutch is exact for Rademacher probes on a matrix with constant diagonal up to the off-diagonal noise."""
+	from primate_b200 import engine
+	from primate_b200.operators import MatrixFunction
+	from primate_b200.trace import hutch
+
+	n = c2.shape[0]
+	M = MatrixFunction(c2, "log", deg=50, orth=0)
+	st, inc = 0x1234567890ABCDEF1234567890ABCDEF, (0xDEADBEEF << 1) | 1
+	y32 = M.quad_block(engine.rademacher_block(st, inc, 64, 32, n, np.float64)).cpu().numpy()
+	y8 = M.quad_block(engine.rademacher_block(st, inc, 72, 8, n, np.float64)).cpu().numpy()
+	y1 = M.quad_block(engine.rademacher_block(st, inc, 95, 1, n, np.float64)).cpu().numpy()
+	assert rel_err(y32[8:16], y8) < 1e-10 and abs(y32[31] / y1[0] - 1) < 1e-10
+	Mi = MatrixFunction(c2, "identity", deg=2, orth=0)
+	est = hutch(Mi, converge="count", count=64, seed=3)
+	assert abs(est / 4e6 - 1) < 5e-3  # tr(A) = 4 n
