@@ -9,7 +9,7 @@
  *  - Plain pointers and sizes only.  Every `*_dev` pointer is CUDA device memory owned by the CALLER (the
  *    Python host side allocates it as torch tensors); the library never allocates on the hot path.
  *  - A "probe block" is a dense n x k panel stored ROW-MAJOR (probe-minor): element (row r, probe p) lives at
- *    X[r*k + p], so the k values of one row are one contiguous, 16-byte-aligned vector.  k must be a power of
+ *    X[r*k + p], so the k values of one row are one contiguous, 32-byte-aligned vector (device pointers of probe blocks must be 32-byte aligned).  k must be a power of
  *    two in [1, 64].  (The reference stores probes F-ordered (N,k), src/primate/random.py:74-78.)
  *  - `stream` is a cudaStream_t passed as void*; all work is enqueued on it and is stream-ordered.  No entry
  *    point synchronises the device unless documented.

@@ -19,6 +19,8 @@ FLAGS = [
 	"-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden", "--expt-relaxed-constexpr",
 	"-I" + INCLUDE, "-I" + CSRC, "-DSLQ_BUILD",
 ]  # fmt: skip
+FLAGS += os.environ.get("SLQ_EXTRA_NVCC_FLAGS", "").split()  # tuning experiments only (e.g. -DSLQ_STEPA_MINB=2)
+LIB = os.environ.get("SLQ_LIB_OUT", LIB)
 
 
 def _stale(target: str, deps: list) -> bool:

@@ -62,7 +62,7 @@ EXPORTED = tuple(_SIGNATURES)
 
 
 def lib_path() -> str:
-	return os.path.join(os.path.dirname(os.path.abspath(__file__)), "libslq.so")
+	return os.environ.get("SLQ_LIB", os.path.join(os.path.dirname(os.path.abspath(__file__)), "libslq.so"))
 
 
 def lib() -> ctypes.CDLL:

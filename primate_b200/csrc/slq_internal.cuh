@@ -75,13 +75,17 @@ struct slq_op {
 
 namespace slq {
 
-// ---- vector packs: V scalars moved with one 4/8/16-byte access -------------------------------------------
+// ---- vector packs: V scalars moved with one 4/8/16/32-byte access -------------------------------------------
 template <typename T, int V>
 struct alignas(sizeof(T) * V) Pack {
   T v[V];
 };
 
 enum CachePolicy { LD_DEFAULT = 0, LD_STREAM = 1, LD_READONLY = 2 };
+
+struct alignas(32) Raw256 {
+  unsigned long long x, y, z, w;
+};
 
 template <int BYTES>
 struct RawBytes;
@@ -97,39 +101,71 @@ template <>
 struct RawBytes<16> {
   using type = uint4;
 };
+template <>
+struct RawBytes<32> {
+  using type = Raw256;
+};
+
+// 256-bit global accesses (sm_100: LDG.E.256 / STG.E.256) with the three cache policies used below.
+template <int POLICY>
+__device__ __forceinline__ Raw256 ld256(const void* p) {
+  Raw256 r;
+  if (POLICY == LD_STREAM)
+    asm volatile("ld.global.cs.v4.b64 {%0,%1,%2,%3}, [%4];" : "=l"(r.x), "=l"(r.y), "=l"(r.z), "=l"(r.w) : "l"(p));
+  else if (POLICY == LD_READONLY)
+    asm volatile("ld.global.nc.v4.b64 {%0,%1,%2,%3}, [%4];" : "=l"(r.x), "=l"(r.y), "=l"(r.z), "=l"(r.w) : "l"(p));
+  else
+    asm volatile("ld.global.v4.b64 {%0,%1,%2,%3}, [%4];" : "=l"(r.x), "=l"(r.y), "=l"(r.z), "=l"(r.w) : "l"(p) : "memory");
+  return r;
+}
+template <bool STREAM>
+__device__ __forceinline__ void st256(void* p, const Raw256& r) {
+  if (STREAM)
+    asm volatile("st.global.cs.v4.b64 [%0], {%1,%2,%3,%4};" ::"l"(p), "l"(r.x), "l"(r.y), "l"(r.z), "l"(r.w) : "memory");
+  else
+    asm volatile("st.global.v4.b64 [%0], {%1,%2,%3,%4};" ::"l"(p), "l"(r.x), "l"(r.y), "l"(r.z), "l"(r.w) : "memory");
+}
 
 // Vector load of V scalars with a cache policy: LD_STREAM = evict-first (read once), LD_READONLY = non-coherent
 // path (re-used panels: the gathered probe rows), LD_DEFAULT = plain.
 template <typename T, int V, int POLICY>
 __device__ __forceinline__ Pack<T, V> ld_pack(const T* p) {
   using R = typename RawBytes<sizeof(T) * V>::type;
-  R raw;
-  if (POLICY == LD_STREAM)
-    raw = __ldcs(reinterpret_cast<const R*>(p));
-  else if (POLICY == LD_READONLY)
-    raw = __ldg(reinterpret_cast<const R*>(p));
-  else
-    raw = *reinterpret_cast<const R*>(p);
   Pack<T, V> out;
-  *reinterpret_cast<R*>(&out) = raw;
+  if constexpr (sizeof(T) * V == 32) {
+    *reinterpret_cast<Raw256*>(&out) = ld256<POLICY>(p);
+  } else {
+    R raw;
+    if (POLICY == LD_STREAM)
+      raw = __ldcs(reinterpret_cast<const R*>(p));
+    else if (POLICY == LD_READONLY)
+      raw = __ldg(reinterpret_cast<const R*>(p));
+    else
+      raw = *reinterpret_cast<const R*>(p);
+    *reinterpret_cast<R*>(&out) = raw;
+  }
   return out;
 }
 
 template <typename T, int V, bool STREAM>
 __device__ __forceinline__ void st_pack(T* p, const Pack<T, V>& x) {
   using R = typename RawBytes<sizeof(T) * V>::type;
-  R raw = *reinterpret_cast<const R*>(&x);
-  if (STREAM)
-    __stcs(reinterpret_cast<R*>(p), raw);
-  else
-    *reinterpret_cast<R*>(p) = raw;
+  if constexpr (sizeof(T) * V == 32) {
+    st256<STREAM>(p, *reinterpret_cast<const Raw256*>(&x));
+  } else {
+    R raw = *reinterpret_cast<const R*>(&x);
+    if (STREAM)
+      __stcs(reinterpret_cast<R*>(p), raw);
+    else
+      *reinterpret_cast<R*>(p) = raw;
+  }
 }
 
-// Probe-block thread mapping for scalar type T and block width K: each thread owns V adjacent probes of a row;
-// LPR threads cover one row.
+// Probe-block thread mapping for scalar type T and block width K: each thread owns V adjacent probes of a row (one
+// 32-byte access); LPR threads cover one row.
 template <typename T, int K>
 struct BlockMap {
-  static constexpr int VMAX = 16 / (int)sizeof(T);
+  static constexpr int VMAX = 32 / (int)sizeof(T);  // 256-bit accesses
   static constexpr int V = K < VMAX ? K : VMAX;
   static constexpr int LPR = K / V;  // threads per row (<= 32 for K <= 64 fp64 / 128 fp32)
   static_assert(LPR <= 32, "block width too large");

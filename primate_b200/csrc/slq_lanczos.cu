@@ -19,6 +19,15 @@
 
 #include "slq_internal.cuh"
 
+// tuning knobs of the staged CSR kernel: resident CTAs per SM asked of ptxas, gathers kept in flight per row
+#ifndef SLQ_STEPA_MINB
+#define SLQ_STEPA_MINB 4
+#endif
+#ifndef SLQ_GATHER_U
+#define SLQ_GATHER_U 5
+#endif
+
+
 namespace slq {
 
 constexpr int MAXK = 64;
@@ -140,7 +149,7 @@ __global__ void __launch_bounds__(NT) k_init(int64_t n, const T* __restrict__ x,
 
 // ---- kernel A: w = (A u_c) r_c - beta_j (u_p r_p);  alpha partials ----------------------------------------
 // CSR SpMM over the probe block fused with the first half of the three-term recurrence.  One thread owns V
-// adjacent probes of a row (16-byte vector gathers); LPR threads cover a row; a CTA sweeps tiles of
+// adjacent probes of a row (32-byte vector accesses); LPR threads cover a row; a CTA sweeps tiles of
 // consecutive rows assigned round-robin so that all CTAs advance through the matrix as one front (keeps the
 // gathered rows of u_c resident in L1/L2 while neighbours re-use them).
 template <typename T, int K, bool FIRST, bool FUSED_CSR>
@@ -210,6 +219,228 @@ __global__ void __launch_bounds__(NT)
   }
   cta_reduce_slots<K, V, LPR, 1>(acc_a, partial + (size_t)blockIdx.x * K, smem);
   if (elect_last_cta(&sc->counter)) finalize<T, K, FIN_ALPHA>(partial, sc, nullptr, scale_c, so, smem);
+}
+
+// ---- CSR row pipeline ------------------------------------------------------------------------------------------
+// A thread owns V adjacent probes of a row (one 16-byte slice of the probe block per gathered row); the LPR threads
+// of a row group sit in one warp.  The un-pipelined loop serialises rowptr -> (colidx, vals) -> X per row: three to
+// five DRAM latencies per row, which is what bounds it (36% of HBM peak measured).  Here the index stream is
+// software-pipelined in registers, with no shared memory and no barriers:
+//   two rows ahead : the row's [s, e) bounds are loaded;
+//   one row ahead  : lane `sub` of the group loads colidx[s + ch*LPR + sub] / vals[...] -- one coalesced load covers
+//                    LPR consecutive non-zeros of the row (CH such loads per lane when LPR is small);
+//   current row    : indices and values are broadcast inside the group by warp shuffles and up to GATHER_U
+//                    16-byte probe-row gathers are issued back to back before the FMAs consume them, in storage
+//                    (column) order.
+// Rows longer than the prefetched chunk fetch their remaining chunks in line.
+template <typename T, int K>
+struct CsrTiling {
+  // gathers use 16-byte slices (the 32-byte packs of the streaming kernels cost too many registers per gather in flight)
+  static constexpr int VMAX = 16 / (int)sizeof(T);
+  static constexpr int V = K < VMAX ? K : VMAX;
+  static constexpr int LPR = K / V;
+  static constexpr int RPC = NT / LPR;  // rows per CTA pass
+  static constexpr int PASSES = RPC >= 256 ? 1 : (RPC >= 128 ? 2 : 4);
+  static constexpr int TILE = RPC * PASSES;
+  static constexpr int CH = LPR >= 8 ? 1 : 8 / LPR;  // (index, value) pairs held per lane
+  static constexpr int CS = CH * LPR;                // non-zeros per prefetched chunk
+  static constexpr int U = LPR < SLQ_GATHER_U ? LPR : SLQ_GATHER_U;
+};
+
+template <typename T>
+__device__ __forceinline__ T shfl_group(T v, int src, int width);
+template <>
+__device__ __forceinline__ int shfl_group<int>(int v, int src, int width) {
+  return __shfl_sync(0xffffffffu, v, src, width);
+}
+template <>
+__device__ __forceinline__ float shfl_group<float>(float v, int src, int width) {
+  return __shfl_sync(0xffffffffu, v, src, width);
+}
+template <>
+__device__ __forceinline__ double shfl_group<double>(double v, int src, int width) {
+  return __shfl_sync(0xffffffffu, v, src, width);
+}
+
+
+template <typename T, int CH>
+struct RowChunk {
+  int c[CH];
+  T a[CH];
+};
+
+template <typename T, int K>
+__device__ __forceinline__ void chunk_load(RowChunk<T, CsrTiling<T, K>::CH>& ck, const int32_t* __restrict__ colidx,
+                                           const T* __restrict__ vals, int first, int e, int sub) {
+  using C = CsrTiling<T, K>;
+#pragma unroll
+  for (int ch = 0; ch < C::CH; ++ch) {
+    const int i = first + ch * C::LPR + sub;
+    const bool on = i < e;
+    ck.c[ch] = on ? __ldg(colidx + i) : 0;
+    ck.a[ch] = on ? __ldg(vals + i) : (T)0;
+  }
+}
+
+// acc += sum over the chunk's first `cnt` non-zeros (cnt_max: warp-uniform upper bound of cnt)
+template <typename T, int K, int V>
+__device__ __forceinline__ void chunk_gather(T (&acc)[V], const RowChunk<T, CsrTiling<T, K>::CH>& ck, const T* __restrict__ X, int slot,
+                                             int cnt, int cnt_max) {
+  using C = CsrTiling<T, K>;
+#pragma unroll
+  for (int ch = 0; ch < C::CH; ++ch) {
+#pragma unroll
+    for (int l = 0; l < C::LPR; l += C::U) {
+      if (ch * C::LPR + l < cnt_max) {  // warp-uniform
+        Pack<T, V> xv[C::U];
+#pragma unroll
+        for (int u = 0; u < C::U; ++u) {
+          if (l + u < C::LPR) {
+            const int c = shfl_group<int>(ck.c[ch], l + u, C::LPR);
+            if (ch * C::LPR + l + u < cnt) {
+              xv[u] = ld_pack<T, V, LD_READONLY>(X + (int64_t)c * K + slot);
+            } else {
+#pragma unroll
+              for (int q = 0; q < V; ++q) xv[u].v[q] = (T)0;
+            }
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < C::U; ++u) {
+          if (l + u < C::LPR) {
+            const T a = shfl_group<T>(ck.a[ch], l + u, C::LPR);  // value broadcast only now: keeps registers free for the gathers
+            if (ch * C::LPR + l + u < cnt) {
+#pragma unroll
+              for (int q = 0; q < V; ++q) acc[q] = fma(a, xv[u].v[q], acc[q]);
+            }
+          }
+        }
+      }
+    }
+  }
+}
+
+enum StepMode { STEP_FIRST = 0, STEP_NEXT = 1, STEP_PLAIN = 2 };  // PLAIN: w = A u_c only (slq_op_matmat)
+
+// ---- kernel A (CSR operators): w = (A u_c) r_c - beta_j (u_p r_p); alpha partials ------------------------------------
+template <typename T, int K, int MODE>
+__global__ void __launch_bounds__(NT, SLQ_STEPA_MINB)
+    k_stepA_csr(int n, const int32_t* __restrict__ rowptr, const int32_t* __restrict__ colidx, const T* __restrict__ vals,
+                const T* __restrict__ uc, const T* __restrict__ up, T* __restrict__ w, LzScal* sc, const double* scale_c,
+                const double* scale_p, double* partial, StepOut so) {
+  using C = CsrTiling<T, K>;
+  constexpr int V = C::V, LPR = C::LPR, RPC = C::RPC, PASSES = C::PASSES, TILE = C::TILE, CS = C::CS;
+  constexpr bool FIRST = (MODE == STEP_FIRST), PLAIN = (MODE == STEP_PLAIN);
+  __shared__ double smem[NT > NWARP * K ? NT : NWARP * K];
+  __shared__ T s_rc[K], s_brp[K];  // per-probe scales: read per row from shared memory instead of living in registers
+
+  const int sub = threadIdx.x % LPR, rloc = threadIdx.x / LPR;
+  const int slot = sub * V;
+  if (!PLAIN) {
+    for (int t = threadIdx.x; t < K; t += NT) {
+      s_rc[t] = (T)scale_c[t];
+      s_brp[t] = FIRST ? (T)0 : (T)(sc->beta[t]) * (T)scale_p[t];
+    }
+    __syncthreads();
+  }
+  double acc_a[1][V];
+#pragma unroll
+  for (int i = 0; i < V; ++i) acc_a[0][i] = 0.0;
+
+  const int ntiles = (n + TILE - 1) / TILE;
+  const int my_tiles = (int)blockIdx.x < ntiles ? (ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+  const int nsteps = my_tiles * PASSES;  // CTA-uniform trip count (shuffles need whole warps)
+  auto row_of = [&](int m) -> int {      // the m-th row this thread visits, or -1
+    if (m >= nsteps) return -1;
+    const long long r = ((long long)blockIdx.x + (long long)(m / PASSES) * gridDim.x) * TILE + (m % PASSES) * RPC + rloc;
+    return r < n ? (int)r : -1;
+  };
+  auto bounds = [&](int r, int& s, int& e) {
+    s = e = 0;
+    if (r >= 0) {
+      s = __ldg(rowptr + r);
+      e = __ldg(rowptr + r + 1);
+    }
+  };
+
+  // pipeline prologue: bounds of rows 0 and 1, chunk of row 0
+  int s0, e0, s1, e1;
+  int r0 = row_of(0), r1 = row_of(1);
+  bounds(r0, s0, e0);
+  bounds(r1, s1, e1);
+  RowChunk<T, C::CH> ck0, ck1;
+  chunk_load<T, K>(ck0, colidx, vals, s0, e0, sub);
+
+  for (int m = 0; m < nsteps; ++m) {
+    // look-ahead: chunk of row m+1 (its bounds arrived during the previous iteration), bounds of row m+2
+    chunk_load<T, K>(ck1, colidx, vals, s1, e1, sub);
+    const int r2 = row_of(m + 2);
+    int s2, e2;
+    bounds(r2, s2, e2);
+
+    const size_t off = (size_t)(r0 >= 0 ? r0 : 0) * K + slot;
+    Pack<T, V> pv;
+    if (!FIRST && !PLAIN && r0 >= 0) pv = ld_pack<T, V, LD_STREAM>(up + off);
+    T acc[V];
+#pragma unroll
+    for (int q = 0; q < V; ++q) acc[q] = (T)0;
+    const int len = e0 - s0;
+    const int len_max = (int)__reduce_max_sync(0xffffffffu, (unsigned)len);
+    chunk_gather<T, K, V>(acc, ck0, uc, slot, len < CS ? len : CS, len_max < CS ? len_max : CS);
+    for (int base = CS; base < len_max; base += CS) {  // long rows: remaining chunks in line (warp-uniform loop)
+      RowChunk<T, C::CH> ck;
+      chunk_load<T, K>(ck, colidx, vals, s0 + base, e0, sub);
+      int cnt = len - base;
+      cnt = cnt < 0 ? 0 : (cnt < CS ? cnt : CS);
+      const int rest = len_max - base;
+      chunk_gather<T, K, V>(acc, ck, uc, slot, cnt, rest < CS ? rest : CS);
+    }
+    if (r0 >= 0) {
+      Pack<T, V> wv;
+      if (PLAIN) {
+#pragma unroll
+        for (int q = 0; q < V; ++q) wv.v[q] = acc[q];
+        st_pack<T, V, true>(w + off, wv);
+      } else {
+        Pack<T, V> qc = ld_pack<T, V, LD_READONLY>(uc + off);  // L1/L2 hit: the row was just gathered by a neighbour
+#pragma unroll
+        for (int q = 0; q < V; ++q) {
+          const T rcq = s_rc[slot + q];
+          wv.v[q] = FIRST ? acc[q] * rcq : acc[q] * rcq - s_brp[slot + q] * pv.v[q];
+          acc_a[0][q] += (double)(qc.v[q] * rcq) * (double)wv.v[q];
+        }
+        st_pack<T, V, false>(w + off, wv);
+      }
+    }
+    // rotate the pipeline
+    r0 = r1, s0 = s1, e0 = e1, ck0 = ck1;
+    r1 = r2, s1 = s2, e1 = e2;
+  }
+  if (!PLAIN) {
+    cta_reduce_slots<K, V, LPR, 1>(acc_a, partial + (size_t)blockIdx.x * K, smem);
+    if (elect_last_cta(&sc->counter)) finalize<T, K, FIN_ALPHA>(partial, sc, nullptr, scale_c, so, smem);
+  }
+}
+
+// Launch helper: persistent grid = resident CTAs per SM (register limited) x SM count.
+template <typename T, int K, int MODE>
+static int launch_stepA_csr(const slq_op* op, const T* uc, const T* up, T* w, LzScal* sc, const double* scale_c, const double* scale_p,
+                            double* partial, const StepOut& so, cudaStream_t st) {
+  using C = CsrTiling<T, K>;
+  const int64_t n = op->n;
+  const int sms = sm_count();
+  static int resident = 0;  // per template instantiation
+  if (resident == 0) {
+    SLQ_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resident, k_stepA_csr<T, K, MODE>, NT, 0));
+    if (resident < 1) resident = 1;
+    if (resident > 8) resident = 8;  // the partial table holds 8 CTAs per SM
+  }
+  int64_t ntiles = (n + C::TILE - 1) / C::TILE;
+  int64_t g = ntiles < (int64_t)sms * resident ? ntiles : (int64_t)sms * resident;
+  k_stepA_csr<T, K, MODE><<<(unsigned)g, NT, 0, st>>>((int)n, op->rowptr, op->colidx, (const T*)op->vals, uc, up, w, sc, scale_c, scale_p,
+                                                      partial, so);
+  SLQ_LAUNCH_CHECK();
+  return SLQ_OK;
 }
 
 // ---- kernel "axpy": v -= coef * u1, then either ||v||^2 or the next projection's dots ------------------------
@@ -459,7 +690,7 @@ static size_t ws_layout(int64_t n, int k, int ncv, int dtype, Workspace* ws, cha
   size_t partial_off = off;
   int sms = sm_count();
   if (sms <= 0) sms = 148;
-  off += align_up(sizeof(double) * 2 * MAXK * (size_t)sms * 4, 256);
+  off += align_up(sizeof(double) * 2 * MAXK * (size_t)sms * 8, 256);
   if (ws) {
     ws->base = base + panels_off;
     ws->panel_bytes = panel;
@@ -475,10 +706,9 @@ template <typename T, int K>
 static int op_apply(slq_op* op, const T* X, T* Y, cudaStream_t st) {
   const int64_t n = op->n;
   if (op->kind == OP_CSR) {
-    constexpr int RPC = NT / BlockMap<T, K>::LPR;
-    int g = grid_for(n, RPC * 4);
-    k_csr_matmat<T, K><<<g, NT, 0, st>>>(n, op->rowptr, op->colidx, (const T*)op->vals, X, Y);
-    SLQ_LAUNCH_CHECK();
+    StepOut so{};
+    int rc = launch_stepA_csr<T, K, STEP_PLAIN>(op, X, X, Y, nullptr, nullptr, nullptr, nullptr, so, st);
+    if (rc != SLQ_OK) return rc;
   } else if (op->kind == OP_DENSE) {
     constexpr int RPC = NT / BlockMap<T, K>::LPR;
     constexpr int RR = RPC >= 128 ? 1 : (128 / RPC > 8 ? 8 : 128 / RPC);
@@ -545,12 +775,9 @@ static int lanczos_impl(slq_op* op, T* X, int deg, double rtol, int orth, int nc
     const double* scp = first ? scale_of(pc) : scale_of(pp);
     const int pslot = prof_begin(PROF_STEPA, st);
     if (op->kind == OP_CSR) {
-      if (first)
-        k_stepA<T, K, true, true><<<g_row, NT, 0, st>>>(n, op->rowptr, op->colidx, (const T*)op->vals, phys[pc], upp, w, ws.sc,
-                                                        scale_of(pc), scp, ws.partial, so);
-      else
-        k_stepA<T, K, false, true><<<g_row, NT, 0, st>>>(n, op->rowptr, op->colidx, (const T*)op->vals, phys[pc], upp, w, ws.sc,
-                                                         scale_of(pc), scp, ws.partial, so);
+      int rc = first ? launch_stepA_csr<T, K, STEP_FIRST>(op, phys[pc], upp, w, ws.sc, scale_of(pc), scp, ws.partial, so, st)
+                     : launch_stepA_csr<T, K, STEP_NEXT>(op, phys[pc], upp, w, ws.sc, scale_of(pc), scp, ws.partial, so, st);
+      if (rc != SLQ_OK) return rc;
     } else {
       int rc = op_apply<T, K>(op, phys[pc], w, st);
       if (rc != SLQ_OK) return rc;
@@ -560,8 +787,8 @@ static int lanczos_impl(slq_op* op, T* X, int deg, double rtol, int orth, int nc
       else
         k_stepA<T, K, false, false><<<g_row, NT, 0, st>>>(n, nullptr, nullptr, nullptr, phys[pc], upp, w, ws.sc, scale_of(pc), scp,
                                                           ws.partial, so);
+      SLQ_LAUNCH_CHECK();
     }
-    SLQ_LAUNCH_CHECK();
     prof_end(PROF_STEPA, pslot, st);
 
     // columns visited by the re-projection: c, c-1, ... cyclically, `orth` of them; unwritten (zero) columns are
@@ -726,7 +953,7 @@ int slq_lanczos(slq_op* op, void* X_dev, int k, int deg, double rtol, int orth, 
   SLQ_REQUIRE(ncv >= 2, "ncv must be at least 2 (lanczos.h:101)");
   SLQ_REQUIRE(orth >= 0, "orth must be non-negative at the C boundary (resolve the policy on the host)");
   SLQ_REQUIRE(is_pow2(k) && k <= MAXK, "block width k=%d must be a power of two in [1,64]", k);
-  SLQ_REQUIRE(((uintptr_t)X_dev & 15) == 0 && ((uintptr_t)workspace_dev & 255) == 0, "X must be 16-byte and workspace 256-byte aligned");
+  SLQ_REQUIRE(((uintptr_t)X_dev & 31) == 0 && ((uintptr_t)workspace_dev & 255) == 0, "X must be 32-byte and workspace 256-byte aligned");
   if (sm_count() <= 0) return fail(SLQ_ERR_CUDA, "no CUDA device");
   size_t need = ws_layout(op->n, k, ncv, op->dtype, nullptr, nullptr);
   SLQ_REQUIRE(workspace_bytes >= need, "workspace too small: %zu < %zu", workspace_bytes, need);
