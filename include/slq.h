@@ -95,6 +95,19 @@ int64_t slq_op_nnz(const slq_op* op);
 /* Y = A X for a probe block (the SpMM on its own; eigen_operators.h:66-99 `matvec`/`matmat`). */
 int slq_op_matmat(slq_op* op, const void* X_dev, void* Y_dev, int k, slq_stream stream);
 
+/* ---- operator ingestion: locality ordering (no reference counterpart; the reference re-converts the matrix to CSC on
+ * every call, src/primate/_lanczos.cpp:89-93) ------------------------------------------------------------------ */
+/* HOST arrays.  perm_out[new] = old: a greedy breadth-first clustering of the symmetric sparsity graph into groups of
+ * `tile` consecutive rows, so that most non-zeros of a row tile point into the tile itself (L1 hits in the SpMM instead
+ * of repeated L2 fetches).  P A P^T has the same spectrum and, started from P x, the same Lanczos coefficients. */
+int slq_csr_cluster_order(int64_t n, const int32_t* rowptr_host, const int32_t* colidx_host, int tile, int32_t* perm_out_host);
+/* HOST arrays.  B = P A P^T for perm[new] = old; output arrays sized like the input; column indices sorted per row. */
+int slq_csr_permute(int64_t n, const int32_t* rowptr_host, const int32_t* colidx_host, const void* vals_host, int dtype,
+                    const int32_t* perm_host, int32_t* rowptr_out_host, int32_t* colidx_out_host, void* vals_out_host);
+/* Device probe blocks: out[r][:] = in[idx[r]][:] (gather) and out[idx[r]][:] = in[r][:] (scatter); in != out. */
+int slq_block_gather_rows(const void* in_dev, const int32_t* idx_dev, int64_t n, int k, int dtype, void* out_dev, slq_stream stream);
+int slq_block_scatter_rows(const void* in_dev, const int32_t* idx_dev, int64_t n, int k, int dtype, void* out_dev, slq_stream stream);
+
 /* ---- probes (src/primate/random.py:22-29,47-80 on NumPy's PCG64) ---------------------------------------- */
 /* Rademacher block: X[r*k + p] = +1 if the MSB of PCG64 raw output #((first_probe+p)*n + r) is set else -1,
  * for the generator whose 128-bit (state, inc) BEFORE any draw are given as {hi, lo} pairs.  Bit-exact with

@@ -12,7 +12,7 @@ CSRC = os.path.join(PKG, "csrc")
 INCLUDE = os.path.join(ROOT, "include")
 OBJ_DIR = os.path.join(PKG, "csrc", "build")
 LIB = os.path.join(PKG, "libslq.so")
-SOURCES = ["slq_api.cu", "slq_lanczos.cu", "slq_probes.cu", "slq_quadrature.cu"]
+SOURCES = ["slq_api.cu", "slq_lanczos.cu", "slq_probes.cu", "slq_quadrature.cu", "slq_reorder.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = [
 	"-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo",
@@ -36,7 +36,7 @@ def get_include() -> str:
 
 
 def build(force: bool = False, verbose: bool = True) -> str:
-	headers = [os.path.join(CSRC, "slq_internal.cuh"), os.path.join(INCLUDE, "slq.h")]
+	headers = [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC)) if f.endswith(".cuh")] + [os.path.join(INCLUDE, "slq.h")]
 	os.makedirs(OBJ_DIR, exist_ok=True)
 	jobs = []
 	for src in SOURCES:

@@ -41,6 +41,10 @@ _SIGNATURES = {
 	"slq_op_dtype": (c_int, [c_void_p]),
 	"slq_op_nnz": (c_int64, [c_void_p]),
 	"slq_op_matmat": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
+	"slq_csr_cluster_order": (c_int, [c_int64, c_void_p, c_void_p, c_int, c_void_p]),
+	"slq_csr_permute": (c_int, [c_int64, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
+	"slq_block_gather_rows": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p, c_void_p]),
+	"slq_block_scatter_rows": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p, c_void_p]),
 	"slq_probes_rademacher": (c_int, [POINTER(c_uint64), POINTER(c_uint64), c_uint64, c_int, c_int64, c_int, c_void_p, c_void_p]),
 	"slq_pcg64_raw": (c_int, [POINTER(c_uint64), POINTER(c_uint64), c_uint64, c_int64, c_void_p, c_void_p]),
 	"slq_block_from_columns": (c_int, [c_void_p, c_int64, c_int, c_int, c_void_p, c_void_p]),

@@ -14,6 +14,8 @@
 // in fixed order by the last CTA to finish, which also runs the scalar recurrence bookkeeping (early break
 // mask, lanczos.h:140).  Dots and norms accumulate in fp64 for both fp32 and fp64 panels.
 #include <cmath>
+#include <cstdlib>
+#include <cstring>
 #include <limits>
 #include <vector>
 
@@ -62,7 +64,7 @@ __device__ __forceinline__ void reduce_partials(const double* partial, int ncta,
     double s = 0.0;
     if (ch < NCH)
       for (int c = ch; c < ncta; c += NCH) s += __ldcg(partial + (size_t)c * NS + slot);
-    smem[t] = s;
+    smem[t] = s;  // one slot per thread (CTAs wider than NT threads pass a scratch of blockDim.x doubles)
     __syncthreads();
     if (t < NS) {
       double r = 0.0;
@@ -443,6 +445,31 @@ static int launch_stepA_csr(const slq_op* op, const T* uc, const T* up, T* w, Lz
   return SLQ_OK;
 }
 
+}  // namespace slq
+#include "slq_stepa_tma.cuh"
+namespace slq {
+
+// Step A for a CSR operator: the TMA-staged kernel where the block width allows it (row slices of 64..512 bytes and
+// 16-byte aligned CSR arrays), the register-pipelined kernel otherwise.  SLQ_STEPA=csr forces the latter (A/B timing).
+static bool use_tma_path() {
+  static int cached = -1;
+  if (cached < 0) {
+    const char* e = getenv("SLQ_STEPA");
+    cached = (e && strcmp(e, "csr") == 0) ? 0 : 1;
+  }
+  return cached == 1;
+}
+
+template <typename T, int K, int MODE>
+static int launch_stepA(const slq_op* op, const T* uc, const T* up, T* w, LzScal* sc, const double* scale_c, const double* scale_p,
+                        double* partial, const StepOut& so, cudaStream_t st) {
+  if constexpr (tma_supported<T, K>()) {
+    const bool aligned = (((uintptr_t)op->colidx | (uintptr_t)op->vals | (uintptr_t)uc | (uintptr_t)up | (uintptr_t)w) & 15) == 0;
+    if (aligned && use_tma_path()) return launch_stepA_tma<T, K, MODE>(op, uc, up, w, sc, scale_c, scale_p, partial, so, st);
+  }
+  return launch_stepA_csr<T, K, MODE>(op, uc, up, w, sc, scale_c, scale_p, partial, so, st);
+}
+
 // ---- kernel "axpy": v -= coef * u1, then either ||v||^2 or the next projection's dots ------------------------
 enum AxpyMode { AX_NORM = 0, AX_DOT_SAME = 1, AX_DOT_OTHER = 2 };
 
@@ -707,7 +734,7 @@ static int op_apply(slq_op* op, const T* X, T* Y, cudaStream_t st) {
   const int64_t n = op->n;
   if (op->kind == OP_CSR) {
     StepOut so{};
-    int rc = launch_stepA_csr<T, K, STEP_PLAIN>(op, X, X, Y, nullptr, nullptr, nullptr, nullptr, so, st);
+    int rc = launch_stepA<T, K, STEP_PLAIN>(op, X, X, Y, nullptr, nullptr, nullptr, nullptr, so, st);
     if (rc != SLQ_OK) return rc;
   } else if (op->kind == OP_DENSE) {
     constexpr int RPC = NT / BlockMap<T, K>::LPR;
@@ -775,8 +802,8 @@ static int lanczos_impl(slq_op* op, T* X, int deg, double rtol, int orth, int nc
     const double* scp = first ? scale_of(pc) : scale_of(pp);
     const int pslot = prof_begin(PROF_STEPA, st);
     if (op->kind == OP_CSR) {
-      int rc = first ? launch_stepA_csr<T, K, STEP_FIRST>(op, phys[pc], upp, w, ws.sc, scale_of(pc), scp, ws.partial, so, st)
-                     : launch_stepA_csr<T, K, STEP_NEXT>(op, phys[pc], upp, w, ws.sc, scale_of(pc), scp, ws.partial, so, st);
+      int rc = first ? launch_stepA<T, K, STEP_FIRST>(op, phys[pc], upp, w, ws.sc, scale_of(pc), scp, ws.partial, so, st)
+                     : launch_stepA<T, K, STEP_NEXT>(op, phys[pc], upp, w, ws.sc, scale_of(pc), scp, ws.partial, so, st);
       if (rc != SLQ_OK) return rc;
     } else {
       int rc = op_apply<T, K>(op, phys[pc], w, st);

@@ -1,0 +1,413 @@
+// Step-A kernel for CSR operators, TMA / mbarrier edition (sm_100a).  Included by slq_lanczos.cu.
+//
+//   w = (A u_c) r_c - beta_j r_p u_p ;  alpha_j partials = <q_c, w>          (lanczos.h:123-129, eigen_operators.h:66-77)
+//
+// One persistent CTA per SM: 15 consumer warps + 1 producer warp.  The producer walks the CTA's row tiles
+// (round-robin over the grid, so all CTAs sweep the matrix as one front and gathered neighbour rows stay in L2) and
+// fills a 3-stage shared-memory ring with bulk async copies (cp.async.bulk -> SASS UBLKCP, completion on an mbarrier):
+//     * the tile's slice of colidx / vals  (CSR bytes: read exactly once, fully coalesced, no registers, no shuffles),
+//     * the tile's own rows of u_c         (the dense probe block of the current Lanczos vector, 30 KB per stage),
+//     * the tile's rows of u_p             (the previous Lanczos vector, 30 KB per stage),
+//     * the tile's row pointers            (plain loads by the producer lanes, one tile ahead of their use).
+// Consumers then run a lean loop per row: index/value from shared memory (broadcast inside the row group); a non-zero
+// whose column lies inside the tile reads its 16-byte probe-row slice from the staged u_c tile, any other column is
+// gathered from global memory through the read-only path; FMAs in storage order (so a sorted CSR row is summed in the
+// order of the reference's column sweep).  R rows x U non-zeros of gathers are in flight per thread.  With the locality
+// ordering of slq_csr_cluster_order ~85% of the non-zeros of a grid operator are tile-local, so DRAM latency is paid by
+// the bulk copies (three stages deep), not by the consumers.
+// Tiles whose non-zero slice exceeds the stage capacity are processed in several chunks (accumulators persist in
+// registers), so arbitrarily long rows (power-law graphs) are handled by the same code.
+#pragma once
+
+namespace slq {
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred P1;\n"
+      "LAB_WAIT:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+      "@P1 bra DONE;\n"
+      "bra LAB_WAIT;\n"
+      "DONE:\n"
+      "}" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+// 1-D bulk async copy global -> shared, completion counted in bytes on `bar` (16-byte aligned addresses and size).
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst_smem)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+
+#ifndef SLQ_TMA_U
+#define SLQ_TMA_U 5  // gathers per row per round
+#endif
+#ifndef SLQ_TMA_R
+#define SLQ_TMA_R 2  // rows per thread processed together
+#endif
+#ifndef SLQ_TMA_PREFETCH
+#define SLQ_TMA_PREFETCH 0  // 1: the producer warp also prefetches the off-tile probe rows of the last issued stage into L2
+#endif
+#ifndef SLQ_TMA_STAGES
+#define SLQ_TMA_STAGES 3
+#endif
+
+template <typename T, int K>
+struct TmaTiling {
+  static constexpr int CW = 15;                        // consumer warps (+1 producer = 512 threads: 128 registers each)
+  static constexpr int CT = CW * 32;                   // consumer threads
+  static constexpr int NTHREADS = CT + 32;             // + producer warp
+  static constexpr int V = 16 / (int)sizeof(T);        // 16-byte slices
+  static constexpr int LPR = K / V;                    // lanes per row
+  static constexpr int RPP = CT / LPR;                 // rows per pass
+  static constexpr int TILE_MAX = 30720 / (K * (int)sizeof(T));  // staged panels of at most 30 KB each
+  static constexpr int TILE = TILE_MAX < 120 ? TILE_MAX : 120;   // rows per tile (= the cluster size of the locality ordering)
+  static constexpr int PASSES = TILE / RPP;
+  static constexpr int R = PASSES % SLQ_TMA_R == 0 ? SLQ_TMA_R : 1;  // rows per thread processed together
+  static constexpr int CAP = 960;                      // non-zeros per stage (8 per row; longer slices go in chunks)
+  static constexpr int STAGES = SLQ_TMA_STAGES;
+  static constexpr int NRP = (TILE + 1 + 31) / 32;     // row pointers per producer lane
+  static constexpr int RP_LEN = NRP * 32;
+  // stage layout (bytes)
+  static constexpr size_t OFF_UC = 0;
+  static constexpr size_t OFF_UP = OFF_UC + (size_t)TILE * K * sizeof(T);
+  static constexpr size_t OFF_VA = OFF_UP + (size_t)TILE * K * sizeof(T);
+  static constexpr size_t OFF_CI = OFF_VA + (size_t)CAP * sizeof(T);
+  static constexpr size_t OFF_RP = OFF_CI + (size_t)CAP * 4;
+  static constexpr size_t OFF_HDR = OFF_RP + (size_t)RP_LEN * 4;
+  static constexpr size_t STAGE_BYTES = (OFF_HDR + 16 + 127) / 128 * 128;
+  static constexpr size_t SMEM_BYTES = STAGE_BYTES * STAGES;
+  static_assert(K % V == 0 && LPR >= 4 && LPR <= 32, "block width not supported by the TMA kernel");
+  static_assert(PASSES >= 1 && PASSES * RPP == TILE, "tile must be a whole number of passes");
+};
+
+template <typename T, int K>
+constexpr bool tma_supported() {
+  return (K * (int)sizeof(T)) >= 64 && (K * (int)sizeof(T)) <= 512;
+}
+
+// Probe-row slice of column c: from the staged tile when c lies in [row0, row0 + TILE), from global memory otherwise.
+template <typename T, int K, int V, int TILE>
+__device__ __forceinline__ Pack<T, V> tma_fetch(int c, int row0, const T* s_uc, const T* __restrict__ X, int slot) {
+  const unsigned loc = (unsigned)(c - row0);
+  if (loc < (unsigned)TILE) return *reinterpret_cast<const Pack<T, V>*>(s_uc + (size_t)loc * K + slot);
+  return ld_pack<T, V, LD_READONLY>(X + (size_t)c * K + slot);
+}
+
+// R rows at once, U gathers per row per round; non-zeros [s[r], e[r]) index the stage's ci/va arrays.
+template <typename T, int K, int V, int U, int R, int TILE>
+__device__ __forceinline__ void tma_gather_rows(T (&acc)[R][V], const int (&s)[R], const int (&e)[R], const int* __restrict__ ci,
+                                                const T* __restrict__ va, const T* s_uc, int row0, const T* __restrict__ X,
+                                                int slot) {
+  int len = 0, lmin = 0x7fffffff;
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    len = max(len, e[r] - s[r]);
+    lmin = min(lmin, e[r] - s[r]);
+  }
+  int i = 0;
+  for (; i + U <= lmin; i += U) {  // full rounds: no predicates
+    Pack<T, V> xv[R][U];
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+#pragma unroll
+      for (int u = 0; u < U; ++u) xv[r][u] = tma_fetch<T, K, V, TILE>(ci[s[r] + i + u], row0, s_uc, X, slot);
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const T a = va[s[r] + i + u];
+#pragma unroll
+        for (int q = 0; q < V; ++q) acc[r][q] = fma(a, xv[r][u].v[q], acc[r][q]);
+      }
+  }
+  for (; i < len; i += U) {  // ragged rounds
+    Pack<T, V> xv[R][U];
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+        if (s[r] + i + u < e[r]) xv[r][u] = tma_fetch<T, K, V, TILE>(ci[s[r] + i + u], row0, s_uc, X, slot);
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+        if (s[r] + i + u < e[r]) {
+          const T a = va[s[r] + i + u];
+#pragma unroll
+          for (int q = 0; q < V; ++q) acc[r][q] = fma(a, xv[r][u].v[q], acc[r][q]);
+        }
+  }
+}
+
+template <typename T, int K, int MODE>
+__global__ void __launch_bounds__(TmaTiling<T, K>::NTHREADS, 1)
+    k_stepA_tma(int n, const int32_t* __restrict__ rowptr, const int32_t* __restrict__ colidx, const T* __restrict__ vals,
+                const T* __restrict__ uc, const T* __restrict__ up, T* __restrict__ w, LzScal* sc, const double* scale_c,
+                const double* scale_p, double* partial, StepOut so) {
+  using C = TmaTiling<T, K>;
+  constexpr int V = C::V, LPR = C::LPR, RPP = C::RPP, PASSES = C::PASSES, TILE = C::TILE, CAP = C::CAP, STAGES = C::STAGES;
+  constexpr int U = SLQ_TMA_U, R = C::R;
+  constexpr bool FIRST = (MODE == STEP_FIRST), PLAIN = (MODE == STEP_PLAIN);
+  constexpr bool HAS_UP = !FIRST && !PLAIN;
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  __shared__ uint64_t bar_full[STAGES], bar_empty[STAGES];
+  constexpr int RED = C::CW * K > C::NTHREADS ? C::CW * K : C::NTHREADS;
+  __shared__ double s_red[RED];  // alpha partials per consumer warp; re-used by the finaliser (one slot per thread)
+  __shared__ T s_rc[K], s_brp[K];
+
+  unsigned char* const base = smem_raw;  // bulk copies need 16-byte alignment only
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&bar_full[s], 1);
+      mbar_init(&bar_empty[s], C::CW);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (!PLAIN) {
+    for (int t = tid; t < K; t += C::NTHREADS) {
+      s_rc[t] = (T)scale_c[t];
+      s_brp[t] = FIRST ? (T)0 : (T)(sc->beta[t]) * (T)scale_p[t];
+    }
+  }
+  __syncthreads();
+
+  const int ntiles = (n + TILE - 1) / TILE;
+  double acc_a[V];
+#pragma unroll
+  for (int q = 0; q < V; ++q) acc_a[q] = 0.0;
+
+  if (warp == C::CW) {
+    // ------------------------------------------------ producer warp ------------------------------------------------
+    int stage = 0;
+    uint32_t phase = 0;
+    int pf_stage = -1, pf_cnt = 0, pf_row0 = 0;  // the stage issued one iteration ago (optional L2 prefetcher)
+    uint32_t pf_phase = 0;
+    // Once the index slice of a stage has landed, touch the probe rows it points at with prefetch.global.L2: the one
+    // first-touch (DRAM) gather per matrix row then costs the consumers an L2 hit instead of a full DRAM round trip.
+    auto prefetch_stage = [&]() {
+      if (pf_stage < 0 || !SLQ_TMA_PREFETCH) return;
+      mbar_wait(&bar_full[pf_stage], pf_phase);
+      const int* p_ci = reinterpret_cast<const int*>(base + (size_t)pf_stage * C::STAGE_BYTES + C::OFF_CI);
+      constexpr int LINES = (K * (int)sizeof(T) + 127) / 128;
+      for (int i = lane; i < pf_cnt * LINES; i += 32) {
+        const int c = p_ci[i / LINES];
+        if ((unsigned)(c - pf_row0) < (unsigned)TILE) continue;  // staged with the tile
+        const char* a = reinterpret_cast<const char*>(uc + (size_t)c * K) + (i % LINES) * 128;
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(a));
+      }
+    };
+    int rpn[C::NRP];  // row pointers of the NEXT tile: loaded one tile ahead so their latency is off the issue path
+    auto load_rowptr = [&](int tile) {
+      const int r0 = tile * TILE;
+      const int nr = min(TILE, n - r0);
+#pragma unroll
+      for (int j = 0; j < C::NRP; ++j) rpn[j] = (tile < ntiles) ? __ldg(rowptr + r0 + min(lane + 32 * j, nr)) : 0;
+    };
+    load_rowptr(blockIdx.x);
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+      const int row0 = tile * TILE;
+      const int nrows = min(TILE, n - row0);
+      int rpv[C::NRP];
+#pragma unroll
+      for (int j = 0; j < C::NRP; ++j) rpv[j] = rpn[j];
+      load_rowptr(tile + gridDim.x);
+      const int segA = __shfl_sync(0xffffffffu, rpv[0], 0);
+      const int segB = __shfl_sync(0xffffffffu, rpv[C::NRP - 1], 31);  // index >= TILE + 1 > nrows: clamped to rowptr[row0+nrows]
+      const int lo0 = segA & ~3;                                      // 16-byte aligned start of the index slice
+      const int nch = max(1, (segB - lo0 + CAP - 1) / CAP);
+      for (int ch = 0; ch < nch; ++ch) {
+        mbar_wait(&bar_empty[stage], phase ^ 1u);
+        unsigned char* S = base + (size_t)stage * C::STAGE_BYTES;
+        int* s_rp = reinterpret_cast<int*>(S + C::OFF_RP);
+        int* s_ci = reinterpret_cast<int*>(S + C::OFF_CI);
+        T* s_va = reinterpret_cast<T*>(S + C::OFF_VA);
+        int* s_hdr = reinterpret_cast<int*>(S + C::OFF_HDR);
+#pragma unroll
+        for (int j = 0; j < C::NRP; ++j) s_rp[lane + 32 * j] = rpv[j];
+        const int lo = lo0 + ch * CAP;
+        const int hi = min(lo + CAP, segB);
+        const int cnt = max(hi - lo, 0);
+        const int nb = cnt & ~3;  // elements moved by the bulk copies; the (< 4) tail goes through the lanes
+        if (lane < cnt - nb) {
+          s_ci[nb + lane] = __ldg(colidx + lo + nb + lane);
+          s_va[nb + lane] = __ldg(vals + lo + nb + lane);
+        }
+        const bool last = (ch == nch - 1);
+        if (lane == 0) {
+          s_hdr[0] = lo;
+          s_hdr[1] = hi;
+          s_hdr[2] = last ? 1 : 0;
+        }
+        __syncwarp();
+        if (lane == 0) {
+          const uint32_t b_ci = (uint32_t)nb * 4u, b_va = (uint32_t)nb * (uint32_t)sizeof(T);
+          const uint32_t b_up = (HAS_UP && last) ? (uint32_t)nrows * K * (uint32_t)sizeof(T) : 0u;
+          const uint32_t b_uc = (uint32_t)nrows * K * (uint32_t)sizeof(T);  // every chunk: in-tile columns read it
+          const uint32_t total = b_ci + b_va + b_up + b_uc;
+          if (total > 0) {
+            mbar_arrive_expect_tx(&bar_full[stage], total);
+            if (nb > 0) {
+              bulk_g2s(s_ci, colidx + lo, b_ci, &bar_full[stage]);
+              bulk_g2s(s_va, vals + lo, b_va, &bar_full[stage]);
+            }
+            bulk_g2s(S + C::OFF_UC, uc + (size_t)row0 * K, b_uc, &bar_full[stage]);
+            if (b_up) bulk_g2s(S + C::OFF_UP, up + (size_t)row0 * K, b_up, &bar_full[stage]);
+          } else {
+            mbar_arrive(&bar_full[stage]);
+          }
+        }
+        __syncwarp();
+        prefetch_stage();  // for the stage issued one iteration ago (its copies have landed by now, or nearly)
+        pf_stage = stage;
+        pf_phase = phase;
+        pf_cnt = cnt;
+        pf_row0 = row0;
+        if (++stage == STAGES) {
+          stage = 0;
+          phase ^= 1u;
+        }
+      }
+    }
+    prefetch_stage();
+  } else {
+    // ------------------------------------------------ consumer warps -----------------------------------------------
+    const int sub = tid % LPR, rloc = tid / LPR;
+    const int slot = sub * V;
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+      const int row0 = tile * TILE;
+      T acc[PASSES][V];
+#pragma unroll
+      for (int ps = 0; ps < PASSES; ++ps)
+#pragma unroll
+        for (int q = 0; q < V; ++q) acc[ps][q] = (T)0;
+      bool last;
+      do {
+        mbar_wait(&bar_full[stage], phase);
+        const unsigned char* S = base + (size_t)stage * C::STAGE_BYTES;
+        const int* s_rp = reinterpret_cast<const int*>(S + C::OFF_RP);
+        const int* s_ci = reinterpret_cast<const int*>(S + C::OFF_CI);
+        const T* s_va = reinterpret_cast<const T*>(S + C::OFF_VA);
+        const T* s_up = reinterpret_cast<const T*>(S + C::OFF_UP);
+        const T* s_uc = reinterpret_cast<const T*>(S + C::OFF_UC);
+        const int* s_hdr = reinterpret_cast<const int*>(S + C::OFF_HDR);
+        const int lo = s_hdr[0], hi = s_hdr[1];
+        last = s_hdr[2] != 0;
+#pragma unroll
+        for (int g = 0; g < PASSES / R; ++g) {
+          int s[R], e[R];
+#pragma unroll
+          for (int r = 0; r < R; ++r) {
+            const int rl = (g * R + r) * RPP + rloc;
+            s[r] = min(max(s_rp[rl], lo), hi) - lo;
+            e[r] = min(max(s_rp[rl + 1], lo), hi) - lo;
+          }
+          T a2[R][V];
+#pragma unroll
+          for (int r = 0; r < R; ++r)
+#pragma unroll
+            for (int q = 0; q < V; ++q) a2[r][q] = acc[g * R + r][q];
+          tma_gather_rows<T, K, V, U, R, TILE>(a2, s, e, s_ci, s_va, s_uc, row0, uc, slot);
+#pragma unroll
+          for (int r = 0; r < R; ++r)
+#pragma unroll
+            for (int q = 0; q < V; ++q) acc[g * R + r][q] = a2[r][q];
+          if (last) {
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+              const int rl = (g * R + r) * RPP + rloc;
+              if (row0 + rl < n) {
+                const size_t off = (size_t)(row0 + rl) * K + slot;
+                Pack<T, V> wv;
+                if (PLAIN) {
+#pragma unroll
+                  for (int q = 0; q < V; ++q) wv.v[q] = a2[r][q];
+                  st_pack<T, V, true>(w + off, wv);
+                } else {
+                  Pack<T, V> pv;
+                  if (HAS_UP) pv = *reinterpret_cast<const Pack<T, V>*>(s_up + (size_t)rl * K + slot);
+                  const Pack<T, V> qcr = *reinterpret_cast<const Pack<T, V>*>(s_uc + (size_t)rl * K + slot);
+#pragma unroll
+                  for (int q = 0; q < V; ++q) {
+                    const T rcq = s_rc[slot + q];
+                    wv.v[q] = FIRST ? a2[r][q] * rcq : a2[r][q] * rcq - s_brp[slot + q] * pv.v[q];
+                    acc_a[q] += (double)(qcr.v[q] * rcq) * (double)wv.v[q];
+                  }
+                  st_pack<T, V, false>(w + off, wv);
+                }
+              }
+            }
+          }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bar_empty[stage]);
+        if (++stage == STAGES) {
+          stage = 0;
+          phase ^= 1u;
+        }
+      } while (!last);
+    }
+  }
+
+  if (!PLAIN) {
+    // deterministic CTA reduction of the alpha partials: row groups inside a warp by shuffles, warps through shared memory
+    if (warp < C::CW) {
+#pragma unroll
+      for (int q = 0; q < V; ++q) {
+        double x = acc_a[q];
+#pragma unroll
+        for (int off = 16; off >= LPR; off >>= 1) x += __shfl_xor_sync(0xffffffffu, x, off);
+        acc_a[q] = x;
+      }
+      if (lane < LPR) {
+#pragma unroll
+        for (int q = 0; q < V; ++q) s_red[warp * K + lane * V + q] = acc_a[q];
+      }
+    }
+    __syncthreads();
+    if (tid < K) {
+      double s = 0.0;
+#pragma unroll
+      for (int wi = 0; wi < C::CW; ++wi) s += s_red[wi * K + tid];
+      partial[(size_t)blockIdx.x * K + tid] = s;
+    }
+    if (elect_last_cta(&sc->counter)) finalize<T, K, FIN_ALPHA>(partial, sc, nullptr, scale_c, so, s_red);
+  }
+}
+
+template <typename T, int K, int MODE>
+static int launch_stepA_tma(const slq_op* op, const T* uc, const T* up, T* w, LzScal* sc, const double* scale_c, const double* scale_p,
+                            double* partial, const StepOut& so, cudaStream_t st) {
+  using C = TmaTiling<T, K>;
+  static bool configured = false;
+  if (!configured) {
+    SLQ_CUDA(cudaFuncSetAttribute(k_stepA_tma<T, K, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM_BYTES));
+    configured = true;
+  }
+  const int n = (int)op->n;
+  const int ntiles = (n + C::TILE - 1) / C::TILE;
+  const int g = ntiles < sm_count() ? ntiles : sm_count();
+  k_stepA_tma<T, K, MODE><<<g, C::NTHREADS, C::SMEM_BYTES, st>>>(n, op->rowptr, op->colidx, (const T*)op->vals, uc, up, w, sc, scale_c,
+                                                                 scale_p, partial, so);
+  SLQ_LAUNCH_CHECK();
+  return SLQ_OK;
+}
+
+}  // namespace slq

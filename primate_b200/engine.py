@@ -5,6 +5,7 @@ Everything here runs on the CUDA device or raises; nothing falls back to NumPy.
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import Any, Optional
 
 import numpy as np
@@ -40,6 +41,24 @@ def _code(np_dtype) -> int:
 	raise TypeError("Only 32- or 64-bit floats are supported.")  # mirrors the pybind11 overload failure
 
 
+REORDER_TILE = 120  # rows per cluster: the row tile of the step-A kernel at k = 32 fp64 (slq_stepa_tma.cuh)
+REORDER_MIN_ROWS = 1 << 16  # below this every probe block fits in L2/L1 anyway
+
+
+def _want_reorder(reorder, n: int, nnz: int) -> bool:
+	"""`reorder`: "auto" (large, sparse operators), True/False, or an int cluster size.  SLQ_REORDER=0/1 overrides "auto"."""
+	import os
+
+	if reorder is None or reorder is False:
+		return False
+	if reorder == "auto":
+		env = os.environ.get("SLQ_REORDER")
+		if env is not None:
+			return env not in ("0", "false", "off", "")
+		return n >= REORDER_MIN_ROWS and nnz <= 64 * n
+	return bool(reorder)
+
+
 class _DevView:
 	"""Exposes a raw device pointer through __cuda_array_interface__ so torch can view it without a copy."""
 
@@ -67,7 +86,7 @@ class DeviceOperator:
 	(slow host-callback path, include/pylinop.h:17-40).  The matrix is uploaded ONCE per operator.
 	"""
 
-	def __init__(self, A: Any, dtype=None):
+	def __init__(self, A: Any, dtype=None, reorder="auto"):
 		import scipy.sparse as sp
 
 		torch = _torch()
@@ -87,11 +106,27 @@ class DeviceOperator:
 			C = A.tocsr()
 			C.sort_indices()
 			assert C.nnz < 2**31 - 1, "nnz must fit int32"
-			rowptr = torch.from_numpy(np.ascontiguousarray(C.indptr, dtype=np.int32)).to(dev, non_blocking=False)
-			colidx = torch.from_numpy(np.ascontiguousarray(C.indices, dtype=np.int32)).to(dev)
-			vals = torch.from_numpy(np.ascontiguousarray(C.data, dtype=self.dtype)).to(dev)
+			ip = np.ascontiguousarray(C.indptr, dtype=np.int32)
+			ix = np.ascontiguousarray(C.indices, dtype=np.int32)
+			va = np.ascontiguousarray(C.data, dtype=self.dtype)
+			self.perm = None
+			if _want_reorder(reorder, self.n, int(C.nnz)):
+				# locality ordering (slq_csr_cluster_order): rows grouped into breadth-first clusters of one SpMM row tile
+				tile = int(reorder) if (isinstance(reorder, int) and not isinstance(reorder, bool) and reorder > 1) else int(os.environ.get("SLQ_REORDER_TILE", REORDER_TILE))
+				perm = np.empty(self.n, dtype=np.int32)
+				_ffi.check(L.slq_csr_cluster_order(self.n, ip.ctypes.data, ix.ctypes.data, tile, perm.ctypes.data))
+				ip2, ix2, va2 = np.empty_like(ip), np.empty_like(ix), np.empty_like(va)
+				_ffi.check(L.slq_csr_permute(self.n, ip.ctypes.data, ix.ctypes.data, va.ctypes.data, self.code, perm.ctypes.data,
+				                             ip2.ctypes.data, ix2.ctypes.data, va2.ctypes.data))  # fmt: skip
+				ip, ix, va = ip2, ix2, va2
+				self.perm = torch.from_numpy(perm).to(dev)
+			rowptr = torch.from_numpy(ip).to(dev, non_blocking=False)
+			colidx = torch.from_numpy(ix).to(dev)
+			vals = torch.from_numpy(va).to(dev)
 			self._keep = [rowptr, colidx, vals]
 			self.h2d_bytes = rowptr.numel() * 4 + colidx.numel() * 4 + vals.numel() * vals.element_size()
+			if self.perm is not None:
+				self.h2d_bytes += self.perm.numel() * 4
 			self.kind, self.nnz = "csr", int(C.nnz)
 			_ffi.check(L.slq_csr_create(self.n, self.nnz, rowptr.data_ptr(), colidx.data_ptr(), vals.data_ptr(), self.code,
 			                            ctypes.byref(self._handle)))  # fmt: skip
@@ -113,6 +148,31 @@ class DeviceOperator:
 			self._cb_error = None
 			_ffi.check(L.slq_callback_create(self.n, self.code, self._cb, None, ctypes.byref(self._handle)))
 		self._ws = {}
+		if not hasattr(self, "perm"):
+			self.perm = None
+
+	# ---- row order: device panels handed to / returned by this class are in the CALLER's row order ---------------------
+	def _to_internal(self, X):
+		"""Caller-order probe block -> the operator's (locality) row order.  Identity without a permutation."""
+		if self.perm is None:
+			return X
+		torch = _torch()
+		Xp = torch.empty_like(X)
+		_ffi.check(_ffi.lib().slq_block_gather_rows(X.data_ptr(), self.perm.data_ptr(), self.n, int(X.shape[-1]), self.code,
+		                                            Xp.data_ptr(), _stream_ptr()))  # fmt: skip
+		return Xp
+
+	def _from_internal(self, Yp):
+		if self.perm is None:
+			return Yp
+		torch = _torch()
+		Y = torch.empty_like(Yp)
+		panels = Yp.reshape(-1, self.n, Yp.shape[-1])
+		outs = Y.reshape(-1, self.n, Yp.shape[-1])
+		for i in range(panels.shape[0]):
+			_ffi.check(_ffi.lib().slq_block_scatter_rows(panels[i].data_ptr(), self.perm.data_ptr(), self.n, int(Yp.shape[-1]), self.code,
+			                                             outs[i].data_ptr(), _stream_ptr()))  # fmt: skip
+		return Y
 
 	# host-callback operator: device panels out to the host, `A.matvec` per column, result back (pylinop.h:32-40)
 	def _callback(self, ctx, x_ptr, y_ptr, n, k, dtype, stream) -> int:
@@ -165,24 +225,38 @@ class DeviceOperator:
 	def matmat(self, X):
 		"""Y = A X for a device probe block X (n, k) row-major (torch tensor)."""
 		torch = _torch()
+		X = self._to_internal(X)
 		Y = torch.empty_like(X)
 		self._check(_ffi.lib().slq_op_matmat(self._handle, X.data_ptr(), Y.data_ptr(), int(X.shape[1]), _stream_ptr()))
-		return Y
+		return self._from_internal(Y)
 
-	def lanczos(self, X, deg: int, rtol: float = 1e-8, orth: int = 0, ncv: int = 2, want_basis: bool = False):
-		"""Blocked Lanczos on the device block X (n, k); X is clobbered.  Returns dict of device tensors."""
+	def lanczos(self, X, deg: int, rtol: float = 1e-8, orth: int = 0, ncv: int = 2, want_basis: bool = False, out: Optional[dict] = None,
+	            internal_basis: bool = False):
+		"""Blocked Lanczos on the device block X (n, k); X is clobbered.  Returns dict of device tensors.
+
+		`out` may carry pre-allocated contiguous device tensors "alpha", "beta" (k, deg+1) and "xnorm2" (k,) -- e.g. row
+		slices of one array holding the tridiagonals of many blocks -- in which case nothing is allocated here and the
+		per-probe step counts are not returned."""
 		torch = _torch()
 		n, k = int(X.shape[0]), int(X.shape[1])
 		assert n == self.n and X.is_contiguous() and X.dtype == _tdtype(self.dtype)
-		alpha = torch.empty((k, deg + 1), dtype=X.dtype, device=X.device)
-		beta = torch.empty((k, deg + 1), dtype=X.dtype, device=X.device)
-		steps = torch.empty(k, dtype=torch.int32, device=X.device)
-		xnorm2 = torch.empty(k, dtype=torch.float64, device=X.device)
+		if out is not None:
+			alpha, beta, xnorm2, steps = out["alpha"], out["beta"], out["xnorm2"], out.get("steps")
+			assert alpha.shape == (k, deg + 1) and beta.shape == (k, deg + 1) and alpha.is_contiguous() and beta.is_contiguous()
+			assert alpha.dtype == X.dtype and xnorm2.dtype == torch.float64 and xnorm2.is_contiguous()
+		else:
+			alpha = torch.empty((k, deg + 1), dtype=X.dtype, device=X.device)
+			beta = torch.empty((k, deg + 1), dtype=X.dtype, device=X.device)
+			steps = torch.empty(k, dtype=torch.int32, device=X.device)
+			xnorm2 = torch.empty(k, dtype=torch.float64, device=X.device)
 		Q = torch.empty((ncv, n, k), dtype=X.dtype, device=X.device) if want_basis else None
+		X = self._to_internal(X)  # (a copy when the operator carries a row permutation; the caller's X is then left intact)
 		ws_ptr, ws_bytes = self.workspace(k, ncv)
 		self._check(_ffi.lib().slq_lanczos(self._handle, X.data_ptr(), k, int(deg), float(rtol), int(orth), int(ncv), alpha.data_ptr(),
-		                                   beta.data_ptr(), steps.data_ptr(), xnorm2.data_ptr(), Q.data_ptr() if want_basis else None,
-		                                   ws_ptr, ws_bytes, _stream_ptr()))  # fmt: skip
+		                                   beta.data_ptr(), steps.data_ptr() if steps is not None else None, xnorm2.data_ptr(),
+		                                   Q.data_ptr() if want_basis else None, ws_ptr, ws_bytes, _stream_ptr()))  # fmt: skip
+		if want_basis and not internal_basis:  # internal_basis: Q stays in the operator's row order (see _from_internal)
+			Q = self._from_internal(Q)
 		return {"alpha": alpha, "beta": beta, "steps": steps, "xnorm2": xnorm2, "Q": Q}
 
 

@@ -47,6 +47,9 @@ def _concat(parts: list):
 
 def _sample_range(sample_block: Callable, lo: int, hi: int, kmax: int):
 	"""Quadrature samples of probes [lo, hi) as one (hi-lo,) array, computed in power-of-two blocks."""
+	ranged = getattr(sample_block, "sample_range", None)
+	if ranged is not None and hi > lo:
+		return ranged(lo, hi - lo, kmax)  # device fast path: one batched Golub-Welsch launch for the whole range
 	parts, first = [], lo
 	for k in engine.block_sizes(hi - lo, kmax):
 		parts.append(sample_block(first, k))
@@ -123,7 +126,11 @@ def _run_batched(sample_block, estimator, converge, batch: int, callback, result
 def _device_sampler(A, stream: ProbeStream):
 	"""probe range -> device quadrature samples for a MatrixFunction (SLQ) or an explicit matrix (x^T A x)."""
 	if isinstance(A, MatrixFunction):
-		return lambda first, k: A.quad_block(stream.block(k, first))
+		def _slq(first: int, k: int):
+			return A.quad_block(stream.block(k, first))
+
+		_slq.sample_range = lambda first, count, kmax: A.quad_range(stream, first, count, kmax)
+		return _slq
 	from .lanczos import device_operator
 
 	dev = device_operator(A, stream.dtype)

@@ -24,6 +24,6 @@ timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -s 636 -c 
 echo "ncu launches exit $?"
 echo "== ncu --set full (k_stepA_csr, k_axpy)"
 $SMALL > $OUT/plain_small2.log 2>&1 &&
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:'k_stepA_csr|k_axpy' -s 620 -c 4 -o $OUT/prof_step $SMALL > $OUT/ncu_full.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:'k_stepA_tma|k_stepA_csr|k_axpy' -s 620 -c 4 -o $OUT/prof_step $SMALL > $OUT/ncu_full.log 2>&1
 echo "ncu full exit $?"
 ls -la $OUT

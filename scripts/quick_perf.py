@@ -49,6 +49,7 @@ def main():
 		      f"algorithmic {bytes_step * ps / ms / 1e6:.1f} GB/s; y[0]={y[0].item():.6f}", flush=True)  # fmt: skip
 	# SpMM alone
 	X = engine.rademacher_block(st, inc, 0, args.k, n, dt)
+	perm, op.perm = op.perm, None  # time the SpMM kernel alone (in the operator's own row order)
 	for rep in range(3):
 		e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 		e0.record()

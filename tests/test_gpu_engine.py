@@ -103,6 +103,94 @@ def test_spmm_random_sparse_and_dense(eng):
 		assert np.allclose(Y, D @ Xk, rtol=1e-11, atol=1e-11)
 
 
+def _ragged_matrix(n, seed, dtype=np.float64, heavy_rows=(0, 7, 1500), heavy_nnz=6000):
+	"""Symmetric CSR with empty rows, a few very long rows (several stage-capacity chunks in the TMA step-A kernel),
+	and n / nnz that are not multiples of any tile size."""
+	rng = np.random.default_rng(seed)
+	S = sp.random(n, n, density=3.0 / n, random_state=seed, format="lil", dtype=np.float64)
+	for r in heavy_rows:
+		if r < n:
+			cols = rng.choice(n, size=min(heavy_nnz, n), replace=False)
+			S[r, cols] = rng.standard_normal(cols.size)
+	S = sp.csr_matrix(S)
+	S = (S + S.T).tolil()
+	for r in (3, 4, 5, n - 1):  # empty rows / columns (also the last row)
+		S[r, :] = 0
+		S[:, r] = 0
+	S = sp.csr_matrix(S).astype(dtype)
+	S.eliminate_zeros()
+	S.sort_indices()
+	return S
+
+
+@pytest.mark.parametrize("k", [8, 16, 32, 64])
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+def test_spmm_ragged_long_rows(eng, k, dtype):
+	"""Empty rows, rows of ~6000 non-zeros (multi-chunk tiles), ragged n: exercised through slq_op_matmat."""
+	A = _ragged_matrix(7013, 17, dtype)
+	assert np.diff(A.indptr).max() > 5000 and np.diff(A.indptr).min() == 0
+	rng = np.random.default_rng(k)
+	X = rng.standard_normal((A.shape[0], k)).astype(dtype)
+	Y = eng.DeviceOperator(A, dtype=dtype).matmat(eng.block_from_columns(X, dtype)).cpu().numpy()
+	ref = (A.astype(np.float64) @ X.astype(np.float64))
+	scale = np.abs(A.astype(np.float64)) @ np.abs(X.astype(np.float64)) + 1.0
+	assert np.max(np.abs(Y - ref) / scale) < (1e-13 if dtype == np.float64 else 2e-5)
+
+
+@pytest.mark.parametrize("k", [16, 32, 64])
+def test_lanczos_ragged_vs_oracle(eng, oracle, k):
+	"""alpha/beta of the blocked device Lanczos on the ragged matrix against the compiled reference, per probe."""
+	A = _ragged_matrix(3001, 5, heavy_rows=(0, 11), heavy_nnz=2900)
+	n = A.shape[0]
+	st, inc = oracle.pcg64_state(3)
+	X = eng.rademacher_block(st, inc, 0, k, n, np.float64)
+	W = X.cpu().numpy().copy()
+	out = eng.DeviceOperator(A).lanczos(X, 12, 1e-8, 0, 2)
+	al, be = out["alpha"].cpu().numpy(), out["beta"].cpu().numpy()
+	for p in (0, k // 2, k - 1):
+		ra, rb, _ = oracle.ref_lanczos(A, W[:, p], 12, 1e-8, 0)
+		assert rel_err(al[p, :12], ra[:12]) < 1e-10 and rel_err(be[p, 1:12], rb[1:12]) < 1e-10
+
+
+@pytest.mark.parametrize("k", [1, 8, 32])
+def test_reordered_operator_matches_natural_order(eng, golden, k):
+	"""A DeviceOperator with a locality permutation gives the same SpMM, alpha/beta and basis in the caller's row order."""
+	A = _L30(golden)
+	n = A.shape[0]
+	rng = np.random.default_rng(k)
+	V = rng.standard_normal((n, k))
+	op_r = eng.DeviceOperator(A, reorder=64)
+	assert op_r.perm is not None and not np.array_equal(op_r.perm.cpu().numpy(), np.arange(n))
+	Y = op_r.matmat(eng.block_from_columns(V, np.float64)).cpu().numpy()
+	assert np.allclose(Y, A @ V, rtol=1e-13, atol=1e-13)
+	op_n = eng.DeviceOperator(A, reorder=False)
+	o_r = op_r.lanczos(eng.block_from_columns(V, np.float64), 20, 1e-8, 3, 20, want_basis=True)
+	o_n = op_n.lanczos(eng.block_from_columns(V, np.float64), 20, 1e-8, 3, 20, want_basis=True)
+	assert rel_err(o_r["alpha"].cpu().numpy(), o_n["alpha"].cpu().numpy()) < 1e-11
+	assert rel_err(o_r["beta"].cpu().numpy(), o_n["beta"].cpu().numpy()) < 1e-11
+	assert np.allclose(o_r["Q"].cpu().numpy(), o_n["Q"].cpu().numpy(), atol=1e-9)
+
+
+def test_reordered_quad_and_matvec_golden(eng, golden):
+	"""MatrixFunction.quad / _matvec through a reordered operator against the reference's values on the same inputs."""
+	from primate_b200.operators import MatrixFunction
+
+	A = _L30(golden)
+	M = MatrixFunction(A, "exp", deg=20, orth=0)
+	M._dev = eng.DeviceOperator(A, reorder=64)
+	Mn = MatrixFunction(A, "exp", deg=20, orth=0)
+	Mn._dev = eng.DeviceOperator(A, reorder=False)
+	rng = np.random.default_rng(0)
+	V = rng.choice([-1.0, 1.0], size=(A.shape[0], 5))
+	assert rel_err(M.quad(V), Mn.quad(V)) < 1e-11
+	y, yn = M._matvec(V[:, 0]), Mn._matvec(V[:, 0])
+	assert np.allclose(y, yn, rtol=1e-9, atol=1e-9)
+	import scipy.sparse.linalg as spla
+
+	ref = spla.expm_multiply(A.tocsc(), V[:, 0])
+	assert np.allclose(np.ravel(y), ref, rtol=1e-6, atol=1e-6 * np.abs(ref).max())
+
+
 @pytest.mark.parametrize("orth,ncv", [(0, 2), (0, 20), (3, 20), (20, 20), (5, 5)])
 def test_lanczos_dense_golden(eng, golden, orth, ncv):
 	A, v = golden["A150"], golden["v42"]
