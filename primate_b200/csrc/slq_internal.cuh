@@ -65,6 +65,7 @@ struct slq_op {
   const int32_t* rowptr;
   const int32_t* colidx;
   const void* vals;
+  int max_row_nnz;  // longest CSR row (computed once at creation; selects the step-A variant with the long-row path)
   // dense
   const void* dense;
   int64_t ld;

@@ -682,6 +682,16 @@ __global__ void k_block_to_cols(const T* __restrict__ X, int64_t n, int k, T* __
   }
 }
 
+// longest row of a CSR operator (slq_csr_create)
+__device__ int g_max_row_nnz;
+__global__ void k_max_row_nnz(int64_t n, const int32_t* __restrict__ rowptr) {
+  int m = 0;
+  for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (int64_t)gridDim.x * blockDim.x)
+    m = max(m, __ldg(rowptr + r + 1) - __ldg(rowptr + r));
+  m = __reduce_max_sync(0xffffffffu, m);
+  if ((threadIdx.x & 31) == 0) atomicMax(&g_max_row_nnz, m);
+}
+
 // ---- host side ------------------------------------------------------------------------------------------------------
 struct Grid {
   int stream_ctas;  // persistent grid for the streaming kernels
@@ -917,6 +927,17 @@ int slq_csr_create(int64_t n, int64_t nnz, const int32_t* rowptr_dev, const int3
   op->rowptr = rowptr_dev;
   op->colidx = colidx_dev;
   op->vals = vals_dev;
+  op->max_row_nnz = INT32_MAX;  // unknown => the variant that can share long rows
+  if (sm_count() > 0) {
+    int zero = 0, mx = 0;
+    if (cudaMemcpyToSymbol(g_max_row_nnz, &zero, sizeof(int)) == cudaSuccess) {
+      const int g = (int)((n + NT - 1) / NT < 4096 ? (n + NT - 1) / NT : 4096);
+      k_max_row_nnz<<<g, NT>>>(n, rowptr_dev);
+      count_launch();
+      if (cudaMemcpyFromSymbol(&mx, g_max_row_nnz, sizeof(int)) == cudaSuccess) op->max_row_nnz = mx;
+    }
+    cudaGetLastError();
+  }
   *out = op;
   return SLQ_OK;
 }

@@ -87,7 +87,9 @@ struct TmaTiling {
   static constexpr size_t OFF_CI = OFF_VA + (size_t)CAP * sizeof(T);
   static constexpr size_t OFF_RP = OFF_CI + (size_t)CAP * 4;
   static constexpr size_t OFF_HDR = OFF_RP + (size_t)RP_LEN * 4;
-  static constexpr size_t STAGE_BYTES = (OFF_HDR + 16 + 127) / 128 * 128;
+  static constexpr int LONG = 64;                      // a row with more non-zeros than this inside one chunk is shared by all row groups
+  static constexpr int MAXLONG = CAP / LONG + 1;
+  static constexpr size_t STAGE_BYTES = (OFF_HDR + 16 + 4 * MAXLONG + 127) / 128 * 128;  // header: lo, hi, last, nlong, long rows
   static constexpr size_t SMEM_BYTES = STAGE_BYTES * STAGES;
   static_assert(K % V == 0 && LPR >= 4 && LPR <= 32, "block width not supported by the TMA kernel");
   static_assert(PASSES >= 1 && PASSES * RPP == TILE, "tile must be a whole number of passes");
@@ -152,7 +154,9 @@ __device__ __forceinline__ void tma_gather_rows(T (&acc)[R][V], const int (&s)[R
   }
 }
 
-template <typename T, int K, int MODE>
+// LONGROWS = false: compiled without the shared long-row path (operators whose longest row has <= LONG non-zeros; the
+// extra live state costs the lean kernel registers -- it spilled and ran 2.4x slower with the path compiled in).
+template <typename T, int K, int MODE, bool LONGROWS>
 __global__ void __launch_bounds__(TmaTiling<T, K>::NTHREADS, 1)
     k_stepA_tma(int n, const int32_t* __restrict__ rowptr, const int32_t* __restrict__ colidx, const T* __restrict__ vals,
                 const T* __restrict__ uc, const T* __restrict__ up, T* __restrict__ w, LzScal* sc, const double* scale_c,
@@ -165,7 +169,10 @@ __global__ void __launch_bounds__(TmaTiling<T, K>::NTHREADS, 1)
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ uint64_t bar_full[STAGES], bar_empty[STAGES];
   constexpr int RED = C::CW * K > C::NTHREADS ? C::CW * K : C::NTHREADS;
-  __shared__ double s_red[RED];  // alpha partials per consumer warp; re-used by the finaliser (one slot per thread)
+  constexpr int SCR = RED * 8 > C::CT * 16 ? RED * 8 : C::CT * 16;
+  __shared__ __align__(16) unsigned char s_scratch[SCR];
+  double* s_red = reinterpret_cast<double*>(s_scratch);  // alpha partials per consumer warp; re-used by the finaliser
+  T* s_part = reinterpret_cast<T*>(s_scratch);           // long rows: one partial probe-row per row group
   __shared__ T s_rc[K], s_brp[K];
 
   unsigned char* const base = smem_raw;  // bulk copies need 16-byte alignment only
@@ -249,10 +256,22 @@ __global__ void __launch_bounds__(TmaTiling<T, K>::NTHREADS, 1)
           s_va[nb + lane] = __ldg(vals + lo + nb + lane);
         }
         const bool last = (ch == nch - 1);
+        __syncwarp();
+        int nlong = 0;  // rows with more than LONG non-zeros inside this chunk: processed by all row groups together
+#pragma unroll
+        for (int j = 0; LONGROWS && j < C::NRP; ++j) {
+          const int idx = lane + 32 * j;
+          bool is_long = false;
+          if (idx < TILE) is_long = (min(s_rp[idx + 1], hi) - max(rpv[j], lo)) > C::LONG;
+          const unsigned bal = __ballot_sync(0xffffffffu, is_long);
+          if (is_long) s_hdr[4 + nlong + __popc(bal & ((1u << lane) - 1u))] = idx;
+          nlong += __popc(bal);
+        }
         if (lane == 0) {
           s_hdr[0] = lo;
           s_hdr[1] = hi;
           s_hdr[2] = last ? 1 : 0;
+          s_hdr[3] = nlong;
         }
         __syncwarp();
         if (lane == 0) {
@@ -310,6 +329,45 @@ __global__ void __launch_bounds__(TmaTiling<T, K>::NTHREADS, 1)
         const int* s_hdr = reinterpret_cast<const int*>(S + C::OFF_HDR);
         const int lo = s_hdr[0], hi = s_hdr[1];
         last = s_hdr[2] != 0;
+        const int nlong = LONGROWS ? s_hdr[3] : 0;  // CTA-uniform
+        if (nlong > 0) {
+          // long rows (power-law hubs): every row group takes a slice of the row's non-zeros, the partial probe rows
+          // meet in shared memory and the owner adds them in group order (deterministic)
+          for (int li = 0; li < nlong; ++li) {
+            const int rl = s_hdr[4 + li];
+            const int s0 = min(max(s_rp[rl], lo), hi) - lo, e0 = min(max(s_rp[rl + 1], lo), hi) - lo;
+            const int slice = (e0 - s0 + RPP - 1) / RPP;
+            int ms[1], me[1];
+            ms[0] = min(s0 + rloc * slice, e0);
+            me[0] = min(ms[0] + slice, e0);
+            T part[1][V];
+#pragma unroll
+            for (int q = 0; q < V; ++q) part[0][q] = (T)0;
+            tma_gather_rows<T, K, V, U, 1, TILE>(part, ms, me, s_ci, s_va, s_uc, row0, uc, slot);
+            Pack<T, V> pp;
+#pragma unroll
+            for (int q = 0; q < V; ++q) pp.v[q] = part[0][q];
+            *reinterpret_cast<Pack<T, V>*>(s_part + (size_t)rloc * K + slot) = pp;
+            asm volatile("bar.sync 1, %0;" ::"n"(C::CT) : "memory");
+            if (rloc == rl % RPP) {
+              T sum[V];
+#pragma unroll
+              for (int q = 0; q < V; ++q) sum[q] = (T)0;
+              for (int gg = 0; gg < RPP; ++gg) {
+                const Pack<T, V> x = *reinterpret_cast<const Pack<T, V>*>(s_part + (size_t)gg * K + slot);
+#pragma unroll
+                for (int q = 0; q < V; ++q) sum[q] += x.v[q];
+              }
+#pragma unroll
+              for (int ps = 0; ps < PASSES; ++ps)
+                if (ps == rl / RPP) {
+#pragma unroll
+                  for (int q = 0; q < V; ++q) acc[ps][q] += sum[q];
+                }
+            }
+            asm volatile("bar.sync 1, %0;" ::"n"(C::CT) : "memory");
+          }
+        }
 #pragma unroll
         for (int g = 0; g < PASSES / R; ++g) {
           int s[R], e[R];
@@ -318,6 +376,7 @@ __global__ void __launch_bounds__(TmaTiling<T, K>::NTHREADS, 1)
             const int rl = (g * R + r) * RPP + rloc;
             s[r] = min(max(s_rp[rl], lo), hi) - lo;
             e[r] = min(max(s_rp[rl + 1], lo), hi) - lo;
+            if (nlong > 0 && e[r] - s[r] > C::LONG) e[r] = s[r];  // done above
           }
           T a2[R][V];
 #pragma unroll
@@ -398,14 +457,19 @@ static int launch_stepA_tma(const slq_op* op, const T* uc, const T* up, T* w, Lz
   using C = TmaTiling<T, K>;
   static bool configured = false;
   if (!configured) {
-    SLQ_CUDA(cudaFuncSetAttribute(k_stepA_tma<T, K, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM_BYTES));
+    SLQ_CUDA(cudaFuncSetAttribute(k_stepA_tma<T, K, MODE, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM_BYTES));
+    SLQ_CUDA(cudaFuncSetAttribute(k_stepA_tma<T, K, MODE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM_BYTES));
     configured = true;
   }
   const int n = (int)op->n;
   const int ntiles = (n + C::TILE - 1) / C::TILE;
   const int g = ntiles < sm_count() ? ntiles : sm_count();
-  k_stepA_tma<T, K, MODE><<<g, C::NTHREADS, C::SMEM_BYTES, st>>>(n, op->rowptr, op->colidx, (const T*)op->vals, uc, up, w, sc, scale_c,
-                                                                 scale_p, partial, so);
+  if (op->max_row_nnz > C::LONG)
+    k_stepA_tma<T, K, MODE, true><<<g, C::NTHREADS, C::SMEM_BYTES, st>>>(n, op->rowptr, op->colidx, (const T*)op->vals, uc, up, w, sc,
+                                                                         scale_c, scale_p, partial, so);
+  else
+    k_stepA_tma<T, K, MODE, false><<<g, C::NTHREADS, C::SMEM_BYTES, st>>>(n, op->rowptr, op->colidx, (const T*)op->vals, uc, up, w, sc,
+                                                                          scale_c, scale_p, partial, so);
   SLQ_LAUNCH_CHECK();
   return SLQ_OK;
 }

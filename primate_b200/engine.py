@@ -151,6 +151,41 @@ class DeviceOperator:
 		if not hasattr(self, "perm"):
 			self.perm = None
 
+	@classmethod
+	def from_device_csr(cls, rowptr, colidx, vals, n: int, dtype=None, reorder=False):
+		"""Operator from CSR arrays that already live on the GPU (torch tensors: int32 rowptr (n+1), int32 colidx, float
+		vals; column indices sorted per row recommended).  No host copy is made unless a locality ordering is asked for
+		(`reorder=True` or a cluster size), which runs on the host (slq_csr_cluster_order / slq_csr_permute)."""
+		torch = _torch()
+		L = _ffi.lib()
+		self = cls.__new__(cls)
+		self.n, self.shape = int(n), (int(n), int(n))
+		self.dtype = np.dtype(dtype) if dtype is not None else np.dtype(str(vals.dtype).replace("torch.", ""))
+		self.code = _code(self.dtype)
+		rowptr = rowptr.to(torch.int32).contiguous()
+		colidx = colidx.to(torch.int32).contiguous()
+		vals = vals.to(_tdtype(self.dtype)).contiguous()
+		assert rowptr.is_cuda and colidx.is_cuda and vals.is_cuda and rowptr.numel() == self.n + 1
+		self.perm, self.h2d_bytes = None, 0
+		if reorder:
+			tile = int(reorder) if (isinstance(reorder, int) and not isinstance(reorder, bool) and reorder > 1) else REORDER_TILE
+			ip, ix, va = rowptr.cpu().numpy(), colidx.cpu().numpy(), vals.cpu().numpy()
+			perm = np.empty(self.n, dtype=np.int32)
+			_ffi.check(L.slq_csr_cluster_order(self.n, ip.ctypes.data, ix.ctypes.data, tile, perm.ctypes.data))
+			ip2, ix2, va2 = np.empty_like(ip), np.empty_like(ix), np.empty_like(va)
+			_ffi.check(L.slq_csr_permute(self.n, ip.ctypes.data, ix.ctypes.data, va.ctypes.data, self.code, perm.ctypes.data,
+			                             ip2.ctypes.data, ix2.ctypes.data, va2.ctypes.data))  # fmt: skip
+			dev = rowptr.device
+			rowptr, colidx, vals = torch.from_numpy(ip2).to(dev), torch.from_numpy(ix2).to(dev), torch.from_numpy(va2).to(dev)
+			self.perm = torch.from_numpy(perm).to(dev)
+		self._keep = [rowptr, colidx, vals]
+		self.kind, self.nnz = "csr", int(colidx.numel())
+		self._handle = ctypes.c_void_p()
+		_ffi.check(L.slq_csr_create(self.n, self.nnz, rowptr.data_ptr(), colidx.data_ptr(), vals.data_ptr(), self.code,
+		                            ctypes.byref(self._handle)))  # fmt: skip
+		self._ws = {}
+		return self
+
 	# ---- row order: device panels handed to / returned by this class are in the CALLER's row order ---------------------
 	def _to_internal(self, X):
 		"""Caller-order probe block -> the operator's (locality) row order.  Identity without a permutation."""
@@ -221,6 +256,12 @@ class DeviceOperator:
 			exc, self._cb_error = self._cb_error, None
 			raise exc
 		_ffi.check(rc)
+
+	def matvec(self, x: np.ndarray) -> np.ndarray:
+		"""Host-array product (makes a DeviceOperator a valid `A` for MatrixFunction / hutch, linear_operator.h:25-29)."""
+		x = np.asarray(x, dtype=self.dtype).reshape(self.n, -1)
+		return block_to_columns(self.matmat(block_from_columns(x, self.dtype))).reshape(-1) if x.shape[1] == 1 else \
+			block_to_columns(self.matmat(block_from_columns(x, self.dtype)))
 
 	def matmat(self, X):
 		"""Y = A X for a device probe block X (n, k) row-major (torch tensor)."""
