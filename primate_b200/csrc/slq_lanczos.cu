@@ -447,6 +447,7 @@ static int launch_stepA_csr(const slq_op* op, const T* uc, const T* up, T* w, Lz
 
 }  // namespace slq
 #include "slq_stepa_tma.cuh"
+#include "slq_dense.cuh"
 namespace slq {
 
 // Step A for a CSR operator: the TMA-staged kernel where the block width allows it (row slices of 64..512 bytes and
@@ -747,6 +748,9 @@ static int op_apply(slq_op* op, const T* X, T* Y, cudaStream_t st) {
     int rc = launch_stepA<T, K, STEP_PLAIN>(op, X, X, Y, nullptr, nullptr, nullptr, nullptr, so, st);
     if (rc != SLQ_OK) return rc;
   } else if (op->kind == OP_DENSE) {
+    if constexpr (dense_tma_supported<T, K>()) {
+      if (dense_tma_ok<T, K>(op, X, Y) && use_tma_path()) return launch_dense_tma<T, K>(op, X, Y, st);
+    }
     constexpr int RPC = NT / BlockMap<T, K>::LPR;
     constexpr int RR = RPC >= 128 ? 1 : (128 / RPC > 8 ? 8 : 128 / RPC);
     int64_t g = (n + RPC * RR - 1) / (RPC * RR);

@@ -103,6 +103,35 @@ def test_spmm_random_sparse_and_dense(eng):
 		assert np.allclose(Y, D @ Xk, rtol=1e-11, atol=1e-11)
 
 
+@pytest.mark.parametrize("k", [4, 8, 16, 32, 64])
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+def test_dense_matmat_tiled_path(eng, k, dtype):
+	"""Dense symmetric operator with n a multiple of 128 (bulk-copy staged kernel for k >= 8) against NumPy."""
+	rng = np.random.default_rng(100 + k)
+	n = 384
+	D = rng.standard_normal((n, n))
+	D = ((D + D.T) / 2).astype(dtype)
+	X = rng.standard_normal((n, k)).astype(dtype)
+	Y = eng.DeviceOperator(D, dtype=dtype).matmat(eng.block_from_columns(X, dtype)).cpu().numpy()
+	ref = D.astype(np.float64) @ X.astype(np.float64)
+	assert np.allclose(Y, ref, rtol=1e-12 if dtype == np.float64 else 2e-4, atol=1e-11 if dtype == np.float64 else 2e-3)
+
+
+def test_lanczos_dense_tiled_vs_oracle(eng, oracle):
+	"""alpha/beta on a dense SPD matrix of order 256 (tiled dense kernel, k = 8) against the compiled reference."""
+	rng = np.random.default_rng(8)
+	B = rng.standard_normal((256, 256))
+	A = B @ B.T / 256 + 0.5 * np.eye(256)
+	st, inc = oracle.pcg64_state(21)
+	X = eng.rademacher_block(st, inc, 0, 8, 256, np.float64)
+	W = X.cpu().numpy().copy()
+	out = eng.DeviceOperator(A).lanczos(X, 15, 1e-8, 0, 2)
+	al, be = out["alpha"].cpu().numpy(), out["beta"].cpu().numpy()
+	for p in (0, 3, 7):
+		ra, rb, _ = oracle.ref_lanczos(A, W[:, p], 15, 1e-8, 0)
+		assert rel_err(al[p, :15], ra[:15]) < 1e-10 and rel_err(be[p, 1:15], rb[1:15]) < 1e-10
+
+
 def _ragged_matrix(n, seed, dtype=np.float64, heavy_rows=(0, 7, 1500), heavy_nnz=6000):
 	"""Symmetric CSR with empty rows, a few very long rows (several stage-capacity chunks in the TMA step-A kernel),
 	and n / nnz that are not multiples of any tile size."""
