@@ -238,6 +238,8 @@ def run_ours(args) -> None:
 
 	if world > 1:
 		os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+		if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+			os.environ["NCCL_DEBUG"] = "WARN"  # keep NCCL's version banner off stdout: rank 0 prints ONE JSON line
 		dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 	from primate_b200 import _ffi, engine, sharding
 	from primate_b200.operators import MatrixFunction
