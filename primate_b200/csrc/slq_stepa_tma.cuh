@@ -208,7 +208,7 @@ __global__ void __launch_bounds__(TmaTiling<T, K>::NTHREADS, 1)
     // Once the index slice of a stage has landed, touch the probe rows it points at with prefetch.global.L2: the one
     // first-touch (DRAM) gather per matrix row then costs the consumers an L2 hit instead of a full DRAM round trip.
     auto prefetch_stage = [&]() {
-      if (pf_stage < 0 || !SLQ_TMA_PREFETCH) return;
+      if (pf_stage < 0 || !(SLQ_TMA_PREFETCH || LONGROWS)) return;  // irregular operators: gathers are mostly off-tile
       mbar_wait(&bar_full[pf_stage], pf_phase);
       const int* p_ci = reinterpret_cast<const int*>(base + (size_t)pf_stage * C::STAGE_BYTES + C::OFF_CI);
       constexpr int LINES = (K * (int)sizeof(T) + 127) / 128;

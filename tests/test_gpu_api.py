@@ -168,3 +168,46 @@ def test_c2_full_size_properties(c2):
 	Mi = MatrixFunction(c2, "identity", deg=2, orth=0)
 	est = hutch(Mi, converge="count", count=64, seed=3)
 	assert abs(est / 4e6 - 1) < 5e-3  # tr(A) = 4 n
+
+
+def test_quad_range_equals_quad_block_and_quad(golden):
+	"""The batched-quadrature range path (one Golub-Welsch launch for many Lanczos blocks) returns bit-identical samples
+	to the per-block path and the reference-facing `quad` on the same probes."""
+	from primate_b200.operators import MatrixFunction
+	from primate_b200.random import ProbeStream
+
+	A = _L30(golden)
+	M = MatrixFunction(A, "log", deg=20, orth=0)
+	stream = ProbeStream(A.shape[0], "rademacher", seed=7, dtype=np.float64)
+	y_range = M.quad_range(stream, 3, 77, 32).cpu().numpy()
+	parts, first = [], 3
+	for k in (32, 32, 8, 4, 1):
+		parts.append(M.quad_block(stream.block(k, first)).cpu().numpy())
+		first += k
+	assert np.array_equal(y_range, np.concatenate(parts))
+	W = np.concatenate([stream.block(k, f).cpu().numpy() for f, k in ((3, 32), (35, 32), (67, 8), (75, 4), (79, 1))], axis=1)
+	assert rel_err(M.quad(W), y_range) < 1e-12
+
+
+def test_device_csr_operator_matches_host_ingestion(golden):
+	"""DeviceOperator.from_device_csr (torch CSR arrays already on the GPU; with and without the locality ordering)
+	against the SciPy ingestion path: SpMM, hutch estimate and the host `matvec` protocol."""
+	import torch
+
+	from primate_b200 import engine
+	from primate_b200.operators import MatrixFunction
+	from primate_b200.trace import hutch
+
+	A = _L30(golden)
+	n = A.shape[0]
+	rp = torch.from_numpy(A.indptr.astype(np.int32)).cuda()
+	ci = torch.from_numpy(A.indices.astype(np.int32)).cuda()
+	va = torch.from_numpy(A.data.astype(np.float64)).cuda()
+	ref = hutch(MatrixFunction(A, "exp", deg=20, orth=0), converge="count", count=64, seed=3)
+	x = np.random.default_rng(0).standard_normal(n)
+	for reorder in (False, 64):
+		op = engine.DeviceOperator.from_device_csr(rp, ci, va, n, dtype=np.float64, reorder=reorder)
+		assert (op.perm is not None) == bool(reorder)
+		assert np.allclose(op.matvec(x), A @ x, rtol=1e-13, atol=1e-13)
+		est = hutch(MatrixFunction(op, "exp", deg=20, orth=0), converge="count", count=64, seed=3)
+		assert abs(est / ref - 1) < 1e-10
