@@ -18,7 +18,7 @@ rank's (count, mean, M2) record per step).  1 probe-step = one Lanczos iteration
   cpu_baseline  the reference's compiled extension (oracle/_ref) driven exactly as hutch drives it, on a bounded
           sample of the same workload on the host cores (N = 1 only).
 
-Working set per block (3 panels of n x 32 fp64 = 768 MB + CSR 64 MB) is far larger than the 126 MB L2, so no L2
+Working set per block (3 panels of n x 64 fp64 = 1.5 GB + CSR 64 MB) is far larger than the 126 MB L2, so no L2
 flush is needed between timed iterations ("inputs larger than L2").
 """
 from __future__ import annotations
@@ -50,7 +50,7 @@ def parse_args():
 	ap.add_argument("--grid", type=int, default=1000, help="Laplacian grid side (C2: 1000 -> n = 1e6)")
 	ap.add_argument("--deg", type=int, default=50)
 	ap.add_argument("--probes", type=int, default=10000, help="probes per rank per step (C2: 10 000)")
-	ap.add_argument("--block", type=int, default=32, help="probes per device block")
+	ap.add_argument("--block", type=int, default=64, help="probes per device block (power of two <= 64)")
 	ap.add_argument("--cpu-probes", type=int, default=0, help="reference arm: probes per worker per step (0 = auto)")
 	ap.add_argument("--cpu-workers", type=int, default=0, help="reference arm: worker processes (0 = all host cores)")
 	ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -411,7 +411,7 @@ def run_ours_report(args, world, ms, value, launches, clk, prof, e2e, rec, n, nn
 		"ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
 		"data": "synthetic",
 		"config": {"workload": workload_name(args), "block": args.block, "parallelism": f"probe-sharded x{world}",
-		           "l2_policy": "inputs larger than L2 (768 MB of panels + 64 MB CSR per block vs 126 MB L2); no flush needed",
+		           "l2_policy": "inputs larger than L2 (3 panels of n x block fp64 = 1.5 GB at block 64, + 64 MB CSR, vs 126 MB L2); no flush needed",
 		           "collective": "one all-gather of (count, mean, M2) per rank per step" if world > 1 else "none"},
 		"e2e": e2e, "gpu_launches": int(launches), "clocks": clk, "roofline": roofline, "cpu_baseline": cpu,
 		"check": {"count": rec[0], "mean_logdet": rec[1], "std": float(np.sqrt(rec[2] / max(rec[0] - 1, 1)))},

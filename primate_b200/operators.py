@@ -116,7 +116,7 @@ class MatrixFunction(LinearOperator):
 			y = torch.from_numpy(np.asarray(vals, dtype=np.float64)).cuda()
 		return (y, out) if keep_tridiag else y
 
-	def quad_range(self, stream, first: int, count: int, kmax: int = 32):
+	def quad_range(self, stream, first: int, count: int, kmax: int = 64):
 		"""Quadrature samples of probes [first, first+count) of a `ProbeStream` -> device tensor (count,).
 
 		The Lanczos blocks run back to back and write their tridiagonals into one (count, deg+1) array; the Golub-Welsch
@@ -191,7 +191,7 @@ class MatrixFunction(LinearOperator):
 		y = np.zeros(m)
 		done = 0
 		last = None
-		for kb in engine.block_sizes(m, 32):
+		for kb in engine.block_sizes(m, 64):
 			yb, last = self.quad_block(engine.block_from_columns(x[:, done : done + kb], self.dtype), keep_tridiag=True)
 			y[done : done + kb] = yb.cpu().numpy()
 			done += kb
