@@ -1,0 +1,239 @@
+"""The workloads of the reference's own test-suite, restated against `primate_b200` on the GPU with the
+reference's thresholds.  Each test names the reference test it mirrors (paths relative to the reference checkout);
+none of them needs the reference at run time."""
+import numpy as np
+import pytest
+from scipy.linalg import eigvalsh_tridiagonal, toeplitz
+from scipy.sparse.linalg import LinearOperator, aslinearoperator
+
+pytestmark = pytest.mark.gpu
+
+
+def _spd(n, rng, lo=None, hi=1.0):
+	from primate_b200.random import symmetric
+
+	ew = rng.uniform(size=n, low=(1.0 / n if lo is None else lo), high=hi)
+	return symmetric(n, pd=True, ew=ew, seed=rng), ew
+
+
+def test_lanczos_full_degree_recovers_spectrum():
+	"""tests/test_lanczos.py:11-20 -- eig(T) == eig(A) for n = deg = orth = 50."""
+	from primate_b200.lanczos import lanczos
+
+	rng = np.random.default_rng(seed=1234)
+	n = 50
+	A = rng.uniform(size=(n, n))
+	A = A @ A.T
+	a, b = lanczos(A, v0=rng.uniform(size=n), deg=n, orth=n)
+	assert np.allclose(eigvalsh_tridiagonal(a, b), np.linalg.eigvalsh(A))
+
+
+def test_rayleigh_ritz_extremes_and_orthonormal_vectors():
+	"""tests/test_lanczos.py:23-34."""
+	from primate_b200.lanczos import rayleigh_ritz
+	from primate_b200.random import symmetric
+
+	rng = np.random.default_rng(seed=1234)
+	n = 50
+	ew = rng.uniform(size=n, low=0, high=1)
+	A = symmetric(n, ew=ew, seed=rng)
+	v0 = rng.uniform(size=n)
+	rw = rayleigh_ritz(A, 20, v0=v0)
+	assert np.isclose(rw.max(), ew.max(), atol=1e-2) and np.isclose(rw.min(), ew.min(), atol=1e-2)
+	rw, rv = rayleigh_ritz(A, 20, v0=v0, return_eigenvectors=True)
+	assert np.allclose(rv.T @ rv, np.eye(len(rw)))
+
+
+@pytest.mark.parametrize("deg", [100, 5])
+def test_krylov_reconstruction_of_Av(deg):
+	"""tests/test_operator.py:10-32 -- ||x|| Q Y diag(theta) Y^T e1 == A x from the basis returned by lanczos()."""
+	from primate_b200.lanczos import lanczos
+	from primate_b200.random import symmetric
+	from primate_b200.tridiag import eigh_tridiag
+
+	rng = np.random.default_rng(1234)
+	n = 100
+	A = symmetric(n)
+	v = rng.uniform(size=n, low=-1, high=1)
+	(a, b), Q = lanczos(A, v0=v, deg=deg, return_basis=True)
+	rw, Y = eigh_tridiag(a, b)
+	z = np.linalg.norm(v) * Q @ (Y @ (rw * Y[0, :]))
+	assert np.isclose(np.linalg.norm(z - A @ v), 0.0)
+
+
+def test_quad_is_the_exact_quadratic_form_for_identity():
+	"""tests/test_operator.py:35-46 -- M.quad(V) == diag(V^T A V), deg = orth = n."""
+	from primate_b200.operators import MatrixFunction
+	from primate_b200.random import symmetric
+
+	rng = np.random.default_rng(1234)
+	n = 100
+	A = symmetric(n)
+	M = MatrixFunction(A, deg=n, orth=n, dtype=np.float64)
+	assert len(M.quad(rng.uniform(size=n))) == 1
+	V = rng.uniform(size=(n, 10))
+	assert np.allclose(M.quad(V), np.diag(V.T @ A @ V))
+
+
+def test_matvec_equals_manual_krylov_formula_and_operator_protocol():
+	"""tests/test_operator.py:49-69 -- `_matvec` against the manual formula for six degrees; `M @ v`; LinearOperator input."""
+	from primate_b200.lanczos import lanczos
+	from primate_b200.operators import MatrixFunction
+	from primate_b200.random import symmetric
+	from primate_b200.tridiag import eigh_tridiag
+
+	rng = np.random.default_rng(1234)
+	n = 100
+	A = symmetric(n)
+	for deg in (n, n - 5, n - 10, n - 30, n - 50, n - 75):
+		M = MatrixFunction(A, deg=deg, orth=n, dtype=np.float64)
+		v = rng.uniform(size=n, low=-1, high=1)
+		(a, b), Q = lanczos(A, v0=v, deg=deg, orth=n, return_basis=True)
+		rw, Y = eigh_tridiag(a, b)
+		z2 = np.linalg.norm(v) * Q @ (Y @ (rw * Y[0, :]))
+		assert np.allclose(M._matvec(v.copy()).ravel(), z2)
+	M = MatrixFunction(A, deg=n, orth=n, dtype=np.float64)
+	assert isinstance(M, LinearOperator)
+	assert np.allclose(A @ v, M @ v)  # fails in the reference under SciPy >= 1.12; works here
+	M = MatrixFunction(aslinearoperator(A), deg=n, orth=n, dtype=np.float64)
+	assert np.allclose(A @ v, M @ v)
+
+
+def test_builtin_spectral_functions_against_eigendecomposition():
+	"""tests/test_operator.py:72-83 -- f(A) v for every built-in f, deg = n, on a positive definite matrix."""
+	from primate_b200.operators import MatrixFunction
+	from primate_b200.random import symmetric
+	from primate_b200.special import _BUILTIN_MATRIX_FUNCTIONS, param_callable
+
+	rng = np.random.default_rng(1234)
+	n = 100
+	A = symmetric(n, pd=True)
+	v = rng.uniform(size=n, low=-1, high=1)
+	ew, ev = np.linalg.eigh(A)
+	for fun in _BUILTIN_MATRIX_FUNCTIONS:
+		f = param_callable(fun)
+		y = ev @ (f(ew) * (ev.T @ v))
+		assert np.allclose(y, MatrixFunction(A, fun=f, deg=n) @ v), fun  # host callable (as the reference test passes it)
+		assert np.allclose(y, MatrixFunction(A, fun=fun, deg=n) @ v), fun  # the same built-in evaluated on the device
+
+
+def test_fttr_weights_equal_squared_first_eigenvector_row():
+	"""tests/test_quadrature.py:55-76 -- FTTR weights == ev[0,:]^2 and sum(theta tau) to 1e-10 on an 8x8 Toeplitz matrix."""
+	from primate_b200.integrate import quadrature
+	from primate_b200.lanczos import lanczos
+
+	rng = np.random.default_rng(1234)
+	n = 8
+	A = toeplitz(np.arange(n)).astype(np.float64)
+	alpha, beta = lanczos(A, v0=rng.uniform(size=n), deg=n, orth=n - 1)
+	a, b = alpha, np.append([0], beta)
+	T = np.diag(a) + np.diag(b[1:], 1) + np.diag(b[1:], -1)
+	ew, ev = np.linalg.eigh(T)
+	nodes, weights = quadrature(a, b, deg=30, quad="fttr")
+	truth = np.ravel(ev[0, :]) ** 2
+	assert np.allclose(weights, truth)
+	assert np.isclose(np.sum(nodes * weights), np.sum(truth * ew), atol=1e-10)
+
+
+def test_gauss_quadrature_mean_estimates_the_trace():
+	"""tests/test_quadrature.py:7-18 -- n * mean of 100 Golub-Welsch quadratures is within 10% of tr(A)."""
+	from primate_b200.integrate import quadrature
+	from primate_b200.lanczos import lanczos
+	from primate_b200.random import symmetric
+
+	rng = np.random.default_rng(1234)
+	n = 30
+	A = symmetric(n, pd=True, seed=rng)
+	ests = []
+	for _ in range(100):
+		v = rng.uniform(size=n, low=-1, high=1)
+		v /= np.linalg.norm(v)
+		a, b = lanczos(A, deg=n, v0=v)
+		nodes, weights = quadrature(a, b, deg=n, quad="gw")
+		ests.append(np.sum(nodes * weights))
+	assert abs(np.mean(ests) * n - A.trace()) <= 0.10 * A.trace()
+
+
+def test_hutch_statistical_bound_result_type_and_callback():
+	"""tests/test_trace.py:8-33."""
+	from primate_b200.estimators import EstimatorResult
+	from primate_b200.trace import hutch
+
+	rng = np.random.default_rng(1234)
+	n = 54
+	A, _ = _spd(n, rng)
+	assert abs(A.trace() - hutch(A, seed=rng)) <= 10 / np.sqrt(n)
+	_, info = hutch(A, seed=rng, full=True)
+	assert isinstance(info, EstimatorResult)
+	calls = []
+	hutch(A, callback=lambda res: calls.append(res.estimate))
+	assert len(calls) > 0
+
+
+def test_hutchpp_statistical_bound():
+	"""tests/test_trace.py:36-45."""
+	from primate_b200.estimators import EstimatorResult
+	from primate_b200.trace import hutchpp
+
+	rng = np.random.default_rng(1234)
+	n = 54
+	A, _ = _spd(n, rng)
+	assert abs(A.trace() - hutchpp(A, m=n, seed=rng)) <= 1 / np.sqrt(n)
+	_, info = hutchpp(A, m=n, seed=rng, full=True)
+	assert isinstance(info, EstimatorResult)
+
+
+def test_hutch_on_matrix_function_identity_equals_hutch_on_matrix():
+	"""tests/test_trace.py:48-57 -- identity f, deg = orth = n, same seed, 150 probes: estimates agree to 1e-6."""
+	from primate_b200.operators import MatrixFunction
+	from primate_b200.trace import hutch
+
+	rng = np.random.default_rng(1234)
+	n = 50
+	A, _ = _spd(n, rng)
+	M = MatrixFunction(A, deg=n, orth=n)
+	assert np.isclose(hutch(A, converge="count", count=150, seed=1234), hutch(M, converge="count", count=150, seed=1234), atol=1e-6)
+
+
+@pytest.mark.parametrize("pdf", ["rademacher", "sphere", "normal"])
+def test_xtrace_batch_sizes(pdf):
+	"""tests/test_trace.py:60-76 -- exact (to 1e-2) once the sketch spans the space, for 7 batch sizes and 3 pdfs."""
+	from primate_b200.trace import xtrace
+
+	A = np.random.default_rng(1234).uniform(size=(50, 50))
+	for nb in (1, 2, 3, 5, 10, 20, 50):
+		est = xtrace(A, pdf=pdf, batch=nb, seed=np.random.default_rng(1234), verbose=1, converge="count", count=50)
+		assert np.isclose(abs(A.trace() - est), 0.0, atol=1e-2)
+
+
+def test_xtrace_default_and_callback_trajectory():
+	"""tests/test_trace.py:79-89."""
+	from primate_b200.random import symmetric
+	from primate_b200.trace import xtrace
+
+	rng = np.random.default_rng(1234)
+	A = symmetric(150, pd=True, seed=rng)
+	assert np.isclose(xtrace(A), A.trace(), atol=1e-2)
+	ests = []
+	xtrace(A, batch=1, full=True, seed=rng, callback=lambda res: ests.append(res.estimate))
+	assert np.std(ests) < 0.60
+
+
+def test_diag_tolerance_criterion_and_xdiag_error_decay():
+	"""tests/test_diagonal.py:5-34."""
+	from primate_b200.diagonal import diag, xdiag
+
+	rng = np.random.default_rng(1234)
+	A = rng.normal(size=(50, 50))
+	_, info = diag(A, converge="tolerance", atol=0.10, rtol=0.0, full=True)
+	assert info.criterion(info.estimator) and np.linalg.norm(info.estimator.delta, 2) <= 0.10
+	d = diag(A, converge="tolerance", atol=0.0, rtol=0.001)
+	assert np.linalg.norm(A.diagonal() - d, 2) < 10.0
+
+	A = rng.normal(size=(150, 150))
+	d = xdiag(A, m=10)
+	assert isinstance(d, np.ndarray) and len(d) == 150
+	budget = np.linspace(2, 300, 10).astype(int)
+	errs = [np.linalg.norm(np.diag(A) - xdiag(A, m, pdf="signs", seed=rng)) for m in budget]
+	slope = np.linalg.lstsq(np.c_[budget, np.ones(len(budget))], np.array(errs), rcond=None)[0][0]
+	assert slope < -0.10
