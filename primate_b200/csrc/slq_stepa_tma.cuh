@@ -54,6 +54,9 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src, uint32
 #ifndef SLQ_TMA_U
 #define SLQ_TMA_U 5  // gathers per row per round
 #endif
+#ifndef SLQ_TMA_UB
+#define SLQ_TMA_UB 8  // gathers in flight per thread, non-zero-balanced variant
+#endif
 #ifndef SLQ_TMA_R
 #define SLQ_TMA_R 2  // rows per thread processed together
 #endif
@@ -64,7 +67,8 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src, uint32
 #define SLQ_TMA_STAGES 3
 #endif
 
-template <typename T, int K>
+// BAL: layout of the non-zero-balanced variant (irregular operators): larger index chunks, fewer stages, row sums in smem.
+template <typename T, int K, bool BAL = false>
 struct TmaTiling {
   static constexpr int CW = 15;                        // consumer warps (+1 producer = 512 threads: 128 registers each)
   static constexpr int CT = CW * 32;                   // consumer threads
@@ -76,7 +80,16 @@ struct TmaTiling {
   static constexpr int TILE = TILE_MAX < 120 ? TILE_MAX : 120;   // rows per tile (= the cluster size of the locality ordering)
   static constexpr int PASSES = TILE / RPP;
   static constexpr int R = PASSES % SLQ_TMA_R == 0 ? SLQ_TMA_R : 1;  // rows per thread processed together
-  static constexpr int CAP = 960;                      // non-zeros per stage (8 per row; longer slices go in chunks)
+  static constexpr size_t PANEL = (size_t)TILE * K * sizeof(T);
+  static constexpr size_t BAL_EXTRA = PANEL + (size_t)RPP * 4 + 16;  // balanced variant: row sums + continuation rows
+  static constexpr size_t BAL_BUDGET = 200 * 1024;
+  static constexpr bool bal_fits(int cap, int stages) {
+    return (size_t)stages * (2 * PANEL + (size_t)cap * (sizeof(T) + 4) + 1024) + BAL_EXTRA <= BAL_BUDGET;
+  }
+  // balanced variant: the chunk is the unit of the per-chunk barriers and of the slice bookkeeping, so as large as fits
+  static constexpr int BAL_CAP = bal_fits(3840, 2) ? 3840 : (bal_fits(1920, 2) ? 1920 : 960);
+  static constexpr int BAL_STAGES = bal_fits(BAL_CAP, 3) ? 3 : 2;
+  static constexpr int CAP = BAL ? BAL_CAP : 960;      // non-zeros per stage (lean: 8 per row; longer slices go in chunks)
   static constexpr int STAGES = SLQ_TMA_STAGES;
   static constexpr int NRP = (TILE + 1 + 31) / 32;     // row pointers per producer lane
   static constexpr int RP_LEN = NRP * 32;
@@ -91,6 +104,8 @@ struct TmaTiling {
   static constexpr int MAXLONG = CAP / LONG + 1;
   static constexpr size_t STAGE_BYTES = (OFF_HDR + 16 + 4 * MAXLONG + 127) / 128 * 128;  // header: lo, hi, last, nlong, long rows
   static constexpr size_t SMEM_BYTES = STAGE_BYTES * STAGES;
+  static constexpr size_t SMEM_BAL = STAGE_BYTES * BAL_STAGES + BAL_EXTRA;
+  static_assert(!BAL || SMEM_BAL <= 216 * 1024, "balanced variant does not fit in shared memory");
   static_assert(K % V == 0 && LPR >= 4 && LPR <= 32, "block width not supported by the TMA kernel");
   static_assert(PASSES >= 1 && PASSES * RPP == TILE, "tile must be a whole number of passes");
 };
@@ -157,12 +172,14 @@ __device__ __forceinline__ void tma_gather_rows(T (&acc)[R][V], const int (&s)[R
 // LONGROWS = false: compiled without the shared long-row path (operators whose longest row has <= LONG non-zeros; the
 // extra live state costs the lean kernel registers -- it spilled and ran 2.4x slower with the path compiled in).
 template <typename T, int K, int MODE, bool LONGROWS>
-__global__ void __launch_bounds__(TmaTiling<T, K>::NTHREADS, 1)
+__global__ void __launch_bounds__(TmaTiling<T, K, LONGROWS>::NTHREADS, 1)
     k_stepA_tma(int n, const int32_t* __restrict__ rowptr, const int32_t* __restrict__ colidx, const T* __restrict__ vals,
                 const T* __restrict__ uc, const T* __restrict__ up, T* __restrict__ w, LzScal* sc, const double* scale_c,
                 const double* scale_p, double* partial, StepOut so) {
-  using C = TmaTiling<T, K>;
-  constexpr int V = C::V, LPR = C::LPR, RPP = C::RPP, PASSES = C::PASSES, TILE = C::TILE, CAP = C::CAP, STAGES = C::STAGES;
+  using C = TmaTiling<T, K, LONGROWS>;
+  constexpr int V = C::V, LPR = C::LPR, RPP = C::RPP, PASSES = C::PASSES, TILE = C::TILE, CAP = C::CAP;
+  constexpr int STAGES = LONGROWS ? C::BAL_STAGES : C::STAGES;  // the balanced variant gives stages up for the row accumulators
+  constexpr int UB = SLQ_TMA_UB;
   constexpr int U = SLQ_TMA_U, R = C::R;
   constexpr bool FIRST = (MODE == STEP_FIRST), PLAIN = (MODE == STEP_PLAIN);
   constexpr bool HAS_UP = !FIRST && !PLAIN;
@@ -176,6 +193,8 @@ __global__ void __launch_bounds__(TmaTiling<T, K>::NTHREADS, 1)
   __shared__ T s_rc[K], s_brp[K];
 
   unsigned char* const base = smem_raw;  // bulk copies need 16-byte alignment only
+  T* const s_acc = reinterpret_cast<T*>(smem_raw + (size_t)STAGES * C::STAGE_BYTES);  // balanced variant: TILE x K row sums
+  int* const s_crow = reinterpret_cast<int*>(s_acc + (size_t)TILE * K);                // ... and one continuation row per group
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
   if (tid == 0) {
@@ -185,6 +204,9 @@ __global__ void __launch_bounds__(TmaTiling<T, K>::NTHREADS, 1)
       mbar_init(&bar_empty[s], C::CW);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (LONGROWS) {
+    for (int t = tid; t < TILE * K; t += C::NTHREADS) s_acc[t] = (T)0;
   }
   if (!PLAIN) {
     for (int t = tid; t < K; t += C::NTHREADS) {
@@ -257,21 +279,10 @@ __global__ void __launch_bounds__(TmaTiling<T, K>::NTHREADS, 1)
         }
         const bool last = (ch == nch - 1);
         __syncwarp();
-        int nlong = 0;  // rows with more than LONG non-zeros inside this chunk: processed by all row groups together
-#pragma unroll
-        for (int j = 0; LONGROWS && j < C::NRP; ++j) {
-          const int idx = lane + 32 * j;
-          bool is_long = false;
-          if (idx < TILE) is_long = (min(s_rp[idx + 1], hi) - max(rpv[j], lo)) > C::LONG;
-          const unsigned bal = __ballot_sync(0xffffffffu, is_long);
-          if (is_long) s_hdr[4 + nlong + __popc(bal & ((1u << lane) - 1u))] = idx;
-          nlong += __popc(bal);
-        }
         if (lane == 0) {
           s_hdr[0] = lo;
           s_hdr[1] = hi;
           s_hdr[2] = last ? 1 : 0;
-          s_hdr[3] = nlong;
         }
         __syncwarp();
         if (lane == 0) {
@@ -310,6 +321,7 @@ __global__ void __launch_bounds__(TmaTiling<T, K>::NTHREADS, 1)
     const int slot = sub * V;
     int stage = 0;
     uint32_t phase = 0;
+    if constexpr (!LONGROWS) {
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
       const int row0 = tile * TILE;
       T acc[PASSES][V];
@@ -329,45 +341,6 @@ __global__ void __launch_bounds__(TmaTiling<T, K>::NTHREADS, 1)
         const int* s_hdr = reinterpret_cast<const int*>(S + C::OFF_HDR);
         const int lo = s_hdr[0], hi = s_hdr[1];
         last = s_hdr[2] != 0;
-        const int nlong = LONGROWS ? s_hdr[3] : 0;  // CTA-uniform
-        if (nlong > 0) {
-          // long rows (power-law hubs): every row group takes a slice of the row's non-zeros, the partial probe rows
-          // meet in shared memory and the owner adds them in group order (deterministic)
-          for (int li = 0; li < nlong; ++li) {
-            const int rl = s_hdr[4 + li];
-            const int s0 = min(max(s_rp[rl], lo), hi) - lo, e0 = min(max(s_rp[rl + 1], lo), hi) - lo;
-            const int slice = (e0 - s0 + RPP - 1) / RPP;
-            int ms[1], me[1];
-            ms[0] = min(s0 + rloc * slice, e0);
-            me[0] = min(ms[0] + slice, e0);
-            T part[1][V];
-#pragma unroll
-            for (int q = 0; q < V; ++q) part[0][q] = (T)0;
-            tma_gather_rows<T, K, V, U, 1, TILE>(part, ms, me, s_ci, s_va, s_uc, row0, uc, slot);
-            Pack<T, V> pp;
-#pragma unroll
-            for (int q = 0; q < V; ++q) pp.v[q] = part[0][q];
-            *reinterpret_cast<Pack<T, V>*>(s_part + (size_t)rloc * K + slot) = pp;
-            asm volatile("bar.sync 1, %0;" ::"n"(C::CT) : "memory");
-            if (rloc == rl % RPP) {
-              T sum[V];
-#pragma unroll
-              for (int q = 0; q < V; ++q) sum[q] = (T)0;
-              for (int gg = 0; gg < RPP; ++gg) {
-                const Pack<T, V> x = *reinterpret_cast<const Pack<T, V>*>(s_part + (size_t)gg * K + slot);
-#pragma unroll
-                for (int q = 0; q < V; ++q) sum[q] += x.v[q];
-              }
-#pragma unroll
-              for (int ps = 0; ps < PASSES; ++ps)
-                if (ps == rl / RPP) {
-#pragma unroll
-                  for (int q = 0; q < V; ++q) acc[ps][q] += sum[q];
-                }
-            }
-            asm volatile("bar.sync 1, %0;" ::"n"(C::CT) : "memory");
-          }
-        }
 #pragma unroll
         for (int g = 0; g < PASSES / R; ++g) {
           int s[R], e[R];
@@ -376,7 +349,6 @@ __global__ void __launch_bounds__(TmaTiling<T, K>::NTHREADS, 1)
             const int rl = (g * R + r) * RPP + rloc;
             s[r] = min(max(s_rp[rl], lo), hi) - lo;
             e[r] = min(max(s_rp[rl + 1], lo), hi) - lo;
-            if (nlong > 0 && e[r] - s[r] > C::LONG) e[r] = s[r];  // done above
           }
           T a2[R][V];
 #pragma unroll
@@ -423,6 +395,140 @@ __global__ void __launch_bounds__(TmaTiling<T, K>::NTHREADS, 1)
         }
       } while (!last);
     }
+    } else {
+      // Irregular operators (some row longer than LONG): non-zero-balanced processing.  Rows of any length cost the
+      // same per non-zero; row sums are accumulated in shared memory (s_acc) in a fixed order, hence deterministic.
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+      const int row0 = tile * TILE;
+      bool last;
+      do {
+        mbar_wait(&bar_full[stage], phase);
+        const unsigned char* S = base + (size_t)stage * C::STAGE_BYTES;
+        const int* s_rp = reinterpret_cast<const int*>(S + C::OFF_RP);
+        const int* s_ci = reinterpret_cast<const int*>(S + C::OFF_CI);
+        const T* s_va = reinterpret_cast<const T*>(S + C::OFF_VA);
+        const T* s_up = reinterpret_cast<const T*>(S + C::OFF_UP);
+        const T* s_uc = reinterpret_cast<const T*>(S + C::OFF_UC);
+        const int* s_hdr = reinterpret_cast<const int*>(S + C::OFF_HDR);
+        const int lo = s_hdr[0], hi = s_hdr[1];
+        last = s_hdr[2] != 0;
+        // ---- phase 1: every row group takes an equal slice of the chunk's non-zeros, whatever rows they belong to ----
+        const int vs = max(s_rp[0] - lo, 0), cnt = max(hi - lo, vs);  // [vs, cnt): the chunk's non-zeros of this tile
+        const int per = ((cnt - vs + RPP - 1) / RPP) | 1;  // odd: the row groups of a warp read different smem banks
+        int i = min(vs + rloc * per, cnt);
+        const int end = min(i + per, cnt);
+        int cont_row = -1, r_last = -1;
+        bool last_is_cont = false;
+        if (i < end) {
+          int a = 0, b = TILE;  // largest r with rowptr[r] <= lo + i
+          while (b - a > 1) {
+            const int m = (a + b) >> 1;
+            if (s_rp[m] <= lo + i) a = m; else b = m;
+          }
+          int r = a;
+          int row_end = min(s_rp[r + 1], hi) - lo;
+          bool cont = rloc > 0 && (s_rp[r] - lo) < i;  // the first row began in an earlier slice
+          T part[V];
+#pragma unroll
+          for (int q = 0; q < V; ++q) part[q] = (T)0;
+          // close the row segment held in `part`: a continuation goes to this group's slot of s_part, anything else is
+          // added to the row's sum (only this group adds to a row that begins inside its slice: no race)
+          auto flush = [&]() {
+            Pack<T, V>* dst = reinterpret_cast<Pack<T, V>*>((cont ? s_part + (size_t)rloc * K : s_acc + (size_t)r * K) + slot);
+            Pack<T, V> x;
+            if (cont) {
+#pragma unroll
+              for (int q = 0; q < V; ++q) x.v[q] = part[q];
+              cont_row = r;
+            } else {
+              x = *dst;
+#pragma unroll
+              for (int q = 0; q < V; ++q) x.v[q] += part[q];
+            }
+            *dst = x;
+          };
+          // the slice is walked as a flat list, UB gathers in flight whatever the row lengths are
+          for (; i < end; i += UB) {
+            Pack<T, V> xv[UB];
+#pragma unroll
+            for (int u = 0; u < UB; ++u)
+              if (i + u < end) xv[u] = tma_fetch<T, K, V, TILE>(s_ci[i + u], row0, s_uc, uc, slot);
+#pragma unroll
+            for (int u = 0; u < UB; ++u)
+              if (i + u < end) {
+                if (i + u >= row_end) {
+                  flush();
+                  cont = false;
+#pragma unroll
+                  for (int q = 0; q < V; ++q) part[q] = (T)0;
+                  do {
+                    ++r;
+                    row_end = min(s_rp[r + 1], hi) - lo;
+                  } while (i + u >= row_end && r < TILE - 1);  // skip empty rows
+                }
+                const T av = s_va[i + u];
+#pragma unroll
+                for (int q = 0; q < V; ++q) part[q] = fma(av, xv[u].v[q], part[q]);
+              }
+          }
+          flush();
+          r_last = r;
+          last_is_cont = cont;
+        }
+        if (sub == 0) s_crow[rloc] = cont_row;
+        asm volatile("bar.sync 1, %0;" ::"n"(C::CT) : "memory");
+        // ---- phase 2: the group in whose slice a row begins adds the later slices' partials of that row, in order ----
+        if (r_last >= 0 && !last_is_cont && min(s_rp[r_last + 1], hi) - lo > end) {
+          Pack<T, V>* dst = reinterpret_cast<Pack<T, V>*>(s_acc + (size_t)r_last * K + slot);
+          Pack<T, V> x = *dst;
+          for (int g2 = rloc + 1; g2 < RPP && s_crow[g2] == r_last; ++g2) {
+            const Pack<T, V> y = *reinterpret_cast<const Pack<T, V>*>(s_part + (size_t)g2 * K + slot);
+#pragma unroll
+            for (int q = 0; q < V; ++q) x.v[q] += y.v[q];
+          }
+          *dst = x;
+        }
+        asm volatile("bar.sync 1, %0;" ::"n"(C::CT) : "memory");
+        if (last) {
+#pragma unroll
+          for (int ps = 0; ps < PASSES; ++ps) {
+            const int rl = ps * RPP + rloc;
+            Pack<T, V>* ap = reinterpret_cast<Pack<T, V>*>(s_acc + (size_t)rl * K + slot);
+            const Pack<T, V> av = *ap;
+            Pack<T, V> zero;
+#pragma unroll
+            for (int q = 0; q < V; ++q) zero.v[q] = (T)0;
+            *ap = zero;  // ready for the next tile
+            if (row0 + rl < n) {
+              const size_t off = (size_t)(row0 + rl) * K + slot;
+              Pack<T, V> wv;
+              if (PLAIN) {
+                st_pack<T, V, true>(w + off, av);
+              } else {
+                Pack<T, V> pv;
+                if (HAS_UP) pv = *reinterpret_cast<const Pack<T, V>*>(s_up + (size_t)rl * K + slot);
+                const Pack<T, V> qcr = *reinterpret_cast<const Pack<T, V>*>(s_uc + (size_t)rl * K + slot);
+#pragma unroll
+                for (int q = 0; q < V; ++q) {
+                  const T rcq = s_rc[slot + q];
+                  wv.v[q] = FIRST ? av.v[q] * rcq : av.v[q] * rcq - s_brp[slot + q] * pv.v[q];
+                  acc_a[q] += (double)(qcr.v[q] * rcq) * (double)wv.v[q];
+                }
+                st_pack<T, V, false>(w + off, wv);
+              }
+            }
+          }
+          asm volatile("bar.sync 1, %0;" ::"n"(C::CT) : "memory");  // rows are zeroed before anyone adds to them again
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bar_empty[stage]);
+        if (++stage == STAGES) {
+          stage = 0;
+          phase ^= 1u;
+        }
+      } while (!last);
+    }
+    }
   }
 
   if (!PLAIN) {
@@ -455,17 +561,18 @@ template <typename T, int K, int MODE>
 static int launch_stepA_tma(const slq_op* op, const T* uc, const T* up, T* w, LzScal* sc, const double* scale_c, const double* scale_p,
                             double* partial, const StepOut& so, cudaStream_t st) {
   using C = TmaTiling<T, K>;
+  using CB = TmaTiling<T, K, true>;
   static bool configured = false;
   if (!configured) {
     SLQ_CUDA(cudaFuncSetAttribute(k_stepA_tma<T, K, MODE, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM_BYTES));
-    SLQ_CUDA(cudaFuncSetAttribute(k_stepA_tma<T, K, MODE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM_BYTES));
+    SLQ_CUDA(cudaFuncSetAttribute(k_stepA_tma<T, K, MODE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CB::SMEM_BAL));
     configured = true;
   }
   const int n = (int)op->n;
   const int ntiles = (n + C::TILE - 1) / C::TILE;
   const int g = ntiles < sm_count() ? ntiles : sm_count();
   if (op->max_row_nnz > C::LONG)
-    k_stepA_tma<T, K, MODE, true><<<g, C::NTHREADS, C::SMEM_BYTES, st>>>(n, op->rowptr, op->colidx, (const T*)op->vals, uc, up, w, sc,
+    k_stepA_tma<T, K, MODE, true><<<g, C::NTHREADS, CB::SMEM_BAL, st>>>(n, op->rowptr, op->colidx, (const T*)op->vals, uc, up, w, sc,
                                                                          scale_c, scale_p, partial, so);
   else
     k_stepA_tma<T, K, MODE, false><<<g, C::NTHREADS, C::SMEM_BYTES, st>>>(n, op->rowptr, op->colidx, (const T*)op->vals, uc, up, w, sc,

@@ -59,6 +59,31 @@ def _want_reorder(reorder, n: int, nnz: int) -> bool:
 	return bool(reorder)
 
 
+def _balance_rows_device(rowptr, colidx, vals, n: int, tile: int):
+	"""P A P^T with the rows dealt round-robin to the row tiles by decreasing length, so that every tile (hence every
+	persistent CTA of the step-A kernel) carries about the same number of non-zeros.  Device tensors in and out
+	(index bookkeeping with torch; the SpMM itself is libslq's).  Returns (rowptr, colidx, vals, perm[new] = old)."""
+	torch = _torch()
+	dev = rowptr.device
+	rp = rowptr.long()
+	deg = rp[1:] - rp[:-1]
+	order = torch.argsort(deg, descending=True, stable=True)
+	ntiles = -(-n // tile)
+	pad = torch.full((ntiles * tile - n,), -1, dtype=torch.int64, device=dev)
+	grid = torch.cat([order, pad]).reshape(tile, ntiles).t().reshape(-1)  # rank r -> tile r % ntiles, slot r // ntiles
+	perm = grid[grid >= 0]
+	inv = torch.empty(n, dtype=torch.int64, device=dev)
+	inv[perm] = torch.arange(n, device=dev)
+	ndeg = deg[perm]
+	nrp = torch.zeros(n + 1, dtype=torch.int64, device=dev)
+	nrp[1:] = torch.cumsum(ndeg, 0)
+	nnz = int(nrp[-1].item())
+	src = torch.repeat_interleave(rp[:-1][perm] - nrp[:-1], ndeg) + torch.arange(nnz, device=dev)
+	ncol = inv[colidx.long()[src]].int()
+	nval = vals[src]
+	return nrp.int(), ncol, nval, perm.int()
+
+
 class _DevView:
 	"""Exposes a raw device pointer through __cuda_array_interface__ so torch can view it without a copy."""
 
@@ -84,6 +109,12 @@ class DeviceOperator:
 	Accepts what the reference's FFI accepts (src/primate/_lanczos.cpp:104-111): a dense ndarray, a SciPy sparse
 	matrix/array (any format; converted to CSR once, not per call), or any object with `.matvec` and `.shape`
 	(slow host-callback path, include/pylinop.h:17-40).  The matrix is uploaded ONCE per operator.
+
+	`reorder` (sparse input): "auto" picks a symmetric row/column order for large operators -- breadth-first locality
+	clusters of one SpMM row tile for meshes and the like, or, when the row lengths are heavily skewed (graph hubs),
+	rows dealt to the tiles by decreasing length so that every tile carries the same number of non-zeros
+	("balance").  True / an int cluster size / "balance" force one of them, False keeps the caller's order.  The
+	order is internal: every vector that crosses the API is in the caller's row order.
 	"""
 
 	def __init__(self, A: Any, dtype=None, reorder="auto"):
@@ -110,7 +141,10 @@ class DeviceOperator:
 			ix = np.ascontiguousarray(C.indices, dtype=np.int32)
 			va = np.ascontiguousarray(C.data, dtype=self.dtype)
 			self.perm = None
-			if _want_reorder(reorder, self.n, int(C.nnz)):
+			# power-law row lengths (hubs): no locality to find; deal the rows to the tiles by length instead (on the device)
+			skewed = self.n >= REORDER_MIN_ROWS and int(np.diff(ip).max(initial=0)) > max(1024, 64 * int(C.nnz) // max(self.n, 1))
+			balance = (isinstance(reorder, str) and reorder == "balance") or (isinstance(reorder, str) and reorder == "auto" and skewed and os.environ.get("SLQ_REORDER") is None)
+			if not balance and _want_reorder(reorder, self.n, int(C.nnz)):
 				# locality ordering (slq_csr_cluster_order): rows grouped into breadth-first clusters of one SpMM row tile
 				tile = int(reorder) if (isinstance(reorder, int) and not isinstance(reorder, bool) and reorder > 1) else int(os.environ.get("SLQ_REORDER_TILE", REORDER_TILE))
 				perm = np.empty(self.n, dtype=np.int32)
@@ -123,9 +157,11 @@ class DeviceOperator:
 			rowptr = torch.from_numpy(ip).to(dev, non_blocking=False)
 			colidx = torch.from_numpy(ix).to(dev)
 			vals = torch.from_numpy(va).to(dev)
-			self._keep = [rowptr, colidx, vals]
 			self.h2d_bytes = rowptr.numel() * 4 + colidx.numel() * 4 + vals.numel() * vals.element_size()
-			if self.perm is not None:
+			if balance:
+				rowptr, colidx, vals, self.perm = _balance_rows_device(rowptr, colidx, vals, self.n, REORDER_TILE)
+			self._keep = [rowptr, colidx, vals]
+			if self.perm is not None and not balance:
 				self.h2d_bytes += self.perm.numel() * 4
 			self.kind, self.nnz = "csr", int(C.nnz)
 			_ffi.check(L.slq_csr_create(self.n, self.nnz, rowptr.data_ptr(), colidx.data_ptr(), vals.data_ptr(), self.code,
@@ -155,7 +191,9 @@ class DeviceOperator:
 	def from_device_csr(cls, rowptr, colidx, vals, n: int, dtype=None, reorder=False):
 		"""Operator from CSR arrays that already live on the GPU (torch tensors: int32 rowptr (n+1), int32 colidx, float
 		vals; column indices sorted per row recommended).  No host copy is made unless a locality ordering is asked for
-		(`reorder=True` or a cluster size), which runs on the host (slq_csr_cluster_order / slq_csr_permute)."""
+		(`reorder=True` or a cluster size), which runs on the host (slq_csr_cluster_order / slq_csr_permute).
+		`reorder="balance"` is the ordering for power-law graphs (no locality to find, but hub rows that would pile up in a
+		few row tiles): rows are dealt to the row tiles in order of decreasing length, entirely on the device."""
 		torch = _torch()
 		L = _ffi.lib()
 		self = cls.__new__(cls)
@@ -167,7 +205,9 @@ class DeviceOperator:
 		vals = vals.to(_tdtype(self.dtype)).contiguous()
 		assert rowptr.is_cuda and colidx.is_cuda and vals.is_cuda and rowptr.numel() == self.n + 1
 		self.perm, self.h2d_bytes = None, 0
-		if reorder:
+		if isinstance(reorder, str) and reorder == "balance":
+			rowptr, colidx, vals, self.perm = _balance_rows_device(rowptr, colidx, vals, self.n, REORDER_TILE)
+		elif reorder:
 			tile = int(reorder) if (isinstance(reorder, int) and not isinstance(reorder, bool) and reorder > 1) else REORDER_TILE
 			ip, ix, va = rowptr.cpu().numpy(), colidx.cpu().numpy(), vals.cpu().numpy()
 			perm = np.empty(self.n, dtype=np.int32)

@@ -181,12 +181,15 @@ def c3(args):
 	t0 = time.perf_counter()
 	rowptr, colidx, vals, n, dmax, trace = rmat_laplacian(args.c3_scale)
 	gen_s = time.perf_counter() - t0
-	op = engine.DeviceOperator.from_device_csr(rowptr, colidx, vals, n, dtype=np.float32)
+	t0 = time.perf_counter()
+	op = engine.DeviceOperator.from_device_csr(rowptr, colidx, vals, n, dtype=np.float32, reorder=args.c3_reorder)
+	del rowptr, colidx, vals
+	ingest_s = time.perf_counter() - t0
 	lam = ritz_max(op, np.float32)
 	M = MatrixFunction(op, "exp", deg=30, orth=0, dtype=np.float32, t=-1.0 / lam)
 	probes = args.c3_probes
 	y, ms, same = slq_run(M, np.float32, probes, 32)
-	out = {"config": "C3", "n": n, "nnz": op.nnz, "max_degree": dmax, "lambda_max_ritz": lam, "gen_s": gen_s, "probes": probes, "deg": 30,
+	out = {"config": "C3", "n": n, "nnz": op.nnz, "max_degree": dmax, "lambda_max_ritz": lam, "gen_s": gen_s, "ingest_s": ingest_s, "reorder": str(args.c3_reorder), "probes": probes, "deg": 30,
 	       "ms": ms, "probe_steps_per_s": probes * 30 / ms * 1e3, "deterministic": same, **stats(y)}  # fmt: skip
 	s = 4
 	out["algorithmic_GBps"] = ((op.nnz * (s + 4) + (n + 1) * 4) / 32 + 6 * n * s) * probes * 30 / ms / 1e6
@@ -282,6 +285,7 @@ def main():
 	ap.add_argument("--only", default="C1,C2,C3,C4,C5")
 	ap.add_argument("--c3-scale", type=int, default=24)
 	ap.add_argument("--c3-probes", type=int, default=256)
+	ap.add_argument("--c3-reorder", default="balance", type=lambda v: False if v in ("0", "none", "False") else v)
 	ap.add_argument("--c4-n", type=int, default=32768)
 	ap.add_argument("--c5-grid", type=int, default=256)
 	ap.add_argument("--c5-small", type=int, default=96)

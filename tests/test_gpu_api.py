@@ -190,8 +190,8 @@ def test_quad_range_equals_quad_block_and_quad(golden):
 
 
 def test_device_csr_operator_matches_host_ingestion(golden):
-	"""DeviceOperator.from_device_csr (torch CSR arrays already on the GPU; with and without the locality ordering)
-	against the SciPy ingestion path: SpMM, hutch estimate and the host `matvec` protocol."""
+	"""DeviceOperator.from_device_csr (torch CSR arrays already on the GPU; with and without the locality ordering, and with
+	the row-length balancing order for power-law graphs) against the SciPy ingestion path: SpMM, hutch estimate and the host `matvec` protocol."""
 	import torch
 
 	from primate_b200 import engine
@@ -205,7 +205,7 @@ def test_device_csr_operator_matches_host_ingestion(golden):
 	va = torch.from_numpy(A.data.astype(np.float64)).cuda()
 	ref = hutch(MatrixFunction(A, "exp", deg=20, orth=0), converge="count", count=64, seed=3)
 	x = np.random.default_rng(0).standard_normal(n)
-	for reorder in (False, 64):
+	for reorder in (False, 64, "balance"):
 		op = engine.DeviceOperator.from_device_csr(rp, ci, va, n, dtype=np.float64, reorder=reorder)
 		assert (op.perm is not None) == bool(reorder)
 		assert np.allclose(op.matvec(x), A @ x, rtol=1e-13, atol=1e-13)

@@ -166,6 +166,33 @@ def test_spmm_ragged_long_rows(eng, k, dtype):
 	assert np.max(np.abs(Y - ref) / scale) < (1e-13 if dtype == np.float64 else 2e-5)
 
 
+@pytest.mark.parametrize("dtype,k", [(np.float64, 32), (np.float32, 32), (np.float64, 8), (np.float32, 64)])
+def test_spmm_power_law_graph_laplacian(eng, dtype, k):
+	"""Graph Laplacian with a power-law degree sequence (hubs of ~3000, many rows of 1-100 non-zeros, isolated vertices):
+	the non-zero-balanced step-A variant, rows split over slices and chunks in every possible way."""
+	rng = np.random.default_rng(12)
+	n = 20011
+	w = 1.0 / np.arange(1, n + 1) ** 0.9
+	src = rng.choice(n, size=300000, p=w / w.sum())
+	dst = rng.integers(0, n, size=300000)
+	keep = src != dst
+	W = sp.coo_matrix((np.ones(keep.sum()), (src[keep], dst[keep])), shape=(n, n)).tocsr()
+	W = ((W + W.T) > 0).astype(np.float64)
+	L = (sp.diags(np.asarray(W.sum(axis=1)).ravel()) - W).tocsr().astype(dtype)
+	L.sort_indices()
+	assert np.diff(L.indptr).max() > 2000
+	X = rng.standard_normal((n, k)).astype(dtype)
+	Y = eng.DeviceOperator(L, dtype=dtype, reorder=False).matmat(eng.block_from_columns(X, dtype)).cpu().numpy()
+	ref = L.astype(np.float64) @ X.astype(np.float64)
+	scale = np.abs(L.astype(np.float64)) @ np.abs(X.astype(np.float64)) + 1.0
+	assert np.max(np.abs(Y - ref) / scale) < (1e-13 if dtype == np.float64 else 2e-5)
+	for order in (True, "balance"):  # locality clusters; rows dealt to the tiles by length (the order for such graphs)
+		op = eng.DeviceOperator(L, dtype=dtype, reorder=order)
+		assert op.perm is not None and np.array_equal(np.sort(op.perm.cpu().numpy()), np.arange(n))
+		Y2 = op.matmat(eng.block_from_columns(X, dtype)).cpu().numpy()
+		assert np.max(np.abs(Y2 - ref) / scale) < (1e-13 if dtype == np.float64 else 2e-5)
+
+
 @pytest.mark.parametrize("k", [16, 32, 64])
 def test_lanczos_ragged_vs_oracle(eng, oracle, k):
 	"""alpha/beta of the blocked device Lanczos on the ragged matrix against the compiled reference, per probe."""
