@@ -12,7 +12,7 @@ import numpy as np
 from scipy.sparse.linalg import LinearOperator, aslinearoperator, eigsh
 from scipy.sparse.linalg._interface import IdentityOperator
 
-from . import engine
+from . import engine, sharding
 from .integrate import quadrature  # noqa: F401  (re-exported like the reference module)
 from .lanczos import _lanczos, device_operator  # noqa: F401
 from .special import param_callable
@@ -51,11 +51,15 @@ class MatrixFunction(LinearOperator):
 		orth: number of Lanczos vectors to re-orthogonalise against per step.
 		dtype: float64 or float32.
 		kwargs: parameters of the built-in function (t, a, b, threshold, q).
+		comm (keyword, not in the reference): None (default) keeps block products on this process; "auto" or a
+			torch.distributed group splits the columns of every block product / quadratic form over the ranks (the
+			operator is replicated per GPU; all ranks must then make the same calls; see `sharding.sharded_columns`).
 	"""
 
 	def __init__(self, A: np.ndarray, fun: Optional[Callable] = None, deg: int = 20, orth: int = 3, dtype: np.dtype = F64, **kwargs) -> None:
 		assert is_linear_op(A), "Invalid operator `A`; must be dim=2 symmetric operator with defined matvec"
 		assert deg >= 2, "Degree must be >= 2"
+		comm = kwargs.pop("comm", None)
 		super().__init__(dtype=np.dtype(dtype), shape=tuple(A.shape))  # SciPy >= 1.12 needs this for `M @ v` (SURVEY fact 8)
 		if fun is None or isinstance(fun, str):
 			host_fun = param_callable(fun, **dict(kwargs)) if isinstance(fun, str) else (lambda x: x)
@@ -64,6 +68,7 @@ class MatrixFunction(LinearOperator):
 			host_fun, spec = fun, None
 		self.fun = host_fun
 		self._fun_spec = spec
+		self._comm = sharding.resolve_comm(comm)
 		self._deg = min(deg, A.shape[0])
 		self._rtol = 1e-8
 		self._orth = self._deg if orth < 0 or orth > self._deg else orth
@@ -172,29 +177,87 @@ class MatrixFunction(LinearOperator):
 
 	def _matmat(self, X: np.ndarray):
 		X = np.asarray(X).astype(self.dtype)
+		if self._comm.size > 1 and X.shape[1] > 1:
+			if self._comm.backend == "nccl":
+				return self._matmat_sharded(X)
+			return sharding.sharded_columns(self._matmat_local, X, self._comm).astype(self.dtype, copy=False)
+		return self._matmat_local(X)
+
+	def _matmat_sharded(self, X: np.ndarray):
+		"""Columns split over the ranks: each rank uploads and runs its own column range, the result panels
+		are all-gathered on the devices (NCCL over NVLink) and downloaded once."""
+		import torch
+
 		n, m = X.shape
-		out = np.empty((n, m), dtype=self.dtype, order="F")
+		c = self._comm
+		lo, hi = sharding.probe_range(m, c.rank, c.size)
+		per = -(-m // c.size)
+		mine = torch.zeros((per, n), dtype=engine._tdtype(self.dtype), device="cuda")
+		if hi > lo:
+			mine[: hi - lo] = self._matmat_device(X[:, lo:hi])
+		allp = c.all_gather_tensor(mine)  # (size, per, n)
+		if per * c.size == m:
+			return allp.reshape(m, n).cpu().numpy().T
+		parts = [allp[r, : b - a] for r in range(c.size) for a, b in [sharding.probe_range(m, r, c.size)] if b > a]
+		return torch.cat(parts, 0).cpu().numpy().T
+
+	def _device_blocks(self, X: np.ndarray, kmax: int):
+		"""Uploads the host panel X (n, m) ONCE, in the order it has, and yields (first column, k, device probe block)."""
+		import torch
+
+		from . import _ffi
+
+		n, m = X.shape
+		if not X.flags.c_contiguous and not X.flags.f_contiguous and X.strides[1] == X.itemsize:
+			X = np.ascontiguousarray(X)  # a column range of a row-major panel: compact rows, no transpose
+		rowmajor = X.flags.c_contiguous
+		Xd = torch.from_numpy(X if rowmajor else np.asfortranarray(X).T).to("cuda")  # (n, m) row-major or (m, n) columns
 		done = 0
-		kmax = 8 if self._deg * n * 8 * 8 > (8 << 30) else 32  # bound the stored basis (deg x n x k)
 		for kb in engine.block_sizes(m, kmax):
-			Y = self.matmat_block(engine.block_from_columns(X[:, done : done + kb], self.dtype))
-			out[:, done : done + kb] = engine.block_to_columns(Y)
+			if rowmajor:
+				B = Xd[:, done : done + kb].contiguous()  # already the probe-block layout
+			else:
+				B = torch.empty((n, kb), dtype=Xd.dtype, device="cuda")
+				_ffi.check(_ffi.lib().slq_block_from_columns(Xd[done : done + kb].data_ptr(), n, kb, self.device_op.code, B.data_ptr(),
+				                                             engine._stream_ptr()))  # fmt: skip
+			yield done, kb, B
 			done += kb
-		return out
+
+	def _matmat_local(self, X: np.ndarray):
+		"""One upload of the whole panel, blocked device Lanczos over its columns, one download: no host transposes."""
+		return self._matmat_device(X).cpu().numpy().T
+
+	def _matmat_device(self, X: np.ndarray):
+		"""f(A) X for a host panel X (n, m) -> device tensor (m, n) holding the result columns."""
+		import torch
+
+		from . import _ffi
+
+		n, m = X.shape
+		Yt = torch.empty((m, n), dtype=engine._tdtype(self.dtype), device="cuda")  # columns: an F-ordered (n, m) host array
+		kmax = 8 if self._deg * n * 8 * 8 > (8 << 30) else 32  # bound the stored basis (deg x n x k)
+		for done, kb, B in self._device_blocks(X, kmax):
+			Y = self.matmat_block(B)
+			_ffi.check(_ffi.lib().slq_block_to_columns(Y.data_ptr(), n, kb, self.device_op.code, Yt[done : done + kb].data_ptr(),
+			                                           engine._stream_ptr()))  # fmt: skip
+		return Yt
 
 	def quad(self, x: np.ndarray):
 		r"""Estimates the quadratic forms $x \mapsto x^T f(A) x$ of the columns of `x` by Lanczos quadrature
 		(operators.py:126-151).  Returns a float64 array with one entry per column."""
 		x = np.asarray(x).astype(self.dtype)
 		x = np.atleast_2d(x).T if x.ndim == 1 else x
+		if self._comm.size > 1 and x.shape[1] > 1:
+			return sharding.sharded_columns(lambda b: self._quad_local(b)[np.newaxis, :], x, self._comm).ravel()
+		return self._quad_local(x)
+
+	def _quad_local(self, x: np.ndarray):
 		m = x.shape[1]
 		y = np.zeros(m)
-		done = 0
 		last = None
-		for kb in engine.block_sizes(m, 64):
-			yb, last = self.quad_block(engine.block_from_columns(x[:, done : done + kb], self.dtype), keep_tridiag=True)
+		for done, kb, B in self._device_blocks(x, 64):
+			yb, last = self.quad_block(B, keep_tridiag=True)
 			y[done : done + kb] = yb.cpu().numpy()
-			done += kb
 		if last is not None:  # like the reference, leave the last probe's tridiagonal entries on the instance
 			self._alpha[:] = last["alpha"][-1].cpu().numpy()
 			self._beta[:] = last["beta"][-1].cpu().numpy()

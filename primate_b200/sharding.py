@@ -11,6 +11,11 @@ GPUs.  The only exchange is one tiny collective per convergence check:
 * adaptive criteria / `record=True`: the k samples of each rank's block are all-gathered instead, and every rank
   replays the reference's per-sample updates in global probe order, so all ranks stop at the same probe.
 
+Block drivers (`hutchpp`, `xdiag`, any `M @ block` on a `MatrixFunction` built with `comm=`): the COLUMNS of the
+block are independent Lanczos runs too, so they are split the same way (`sharded_columns`): every rank runs its
+contiguous column range and the tall-skinny result panels are all-gathered, after which the small replicated algebra
+(QR, inverse of R, ...) sees bit-identical data on every rank.
+
 The collectives go through `torch.distributed` (NCCL over NVLink on the GPU box, gloo in the CPU tests).
 """
 from __future__ import annotations
@@ -46,6 +51,15 @@ class Comm:
 		out = torch.empty(self.size * t.numel(), dtype=torch.float64, device=t.device)
 		self._dist.all_gather_into_tensor(out, t, group=self.group)
 		return out.cpu().numpy().reshape(self.size, -1)
+
+	def all_gather_tensor(self, t):
+		"""t: tensor on the backend's device, same shape and dtype on every rank -> (size, *t.shape), no host staging."""
+		import torch
+
+		t = t.contiguous()
+		out = torch.empty((self.size,) + tuple(t.shape), dtype=t.dtype, device=t.device)
+		self._dist.all_gather_into_tensor(out, t, group=self.group)
+		return out
 
 	def barrier(self):
 		self._dist.barrier(group=self.group)
@@ -120,3 +134,35 @@ def record_of(samples: np.ndarray) -> tuple:
 def round_blocks(done: int, k: int, rank: int, size: int) -> tuple:
 	"""Adaptive rounds: in the round starting at global probe `done`, rank r owns probes [done + r*k, done + (r+1)*k)."""
 	return done + rank * k, k
+
+
+def sharded_columns(fn, X: np.ndarray, comm, chunk_bytes: int = 1 << 30) -> np.ndarray:
+	"""Y = fn(X) column by column, with the columns of X split over the ranks of `comm` (block drivers).
+
+	`fn` maps an (n, j) host block to an (r, j) host block, column-wise independent (f(A) X, or the quadratic forms of
+	the columns with r = 1).  Every rank must call this with the same X.  Rank r computes the contiguous column range
+	`probe_range(m, r, size)`; the panels are all-gathered (padded to the common width, in pieces of at most
+	`chunk_bytes` per rank) and every rank returns the same full (r, m) array."""
+	X = np.asarray(X)
+	m = X.shape[1]
+	if comm.size <= 1 or m < 2:
+		return np.asarray(fn(X))
+	lo, hi = probe_range(m, comm.rank, comm.size)
+	per = -(-m // comm.size)
+	mine = np.asarray(fn(X[:, lo:hi])) if hi > lo else None
+	rows = comm.all_gather(np.array([0.0 if mine is None else float(mine.shape[0])])).max()
+	rows = int(rows)
+	dtype = mine.dtype if mine is not None else X.dtype
+	out = np.empty((rows, m), dtype=dtype, order="F")
+	step = max(1, int(chunk_bytes // max(1, per * 8)))  # rows per piece
+	for r0 in range(0, rows, step):
+		r1 = min(rows, r0 + step)
+		pad = np.zeros((per, r1 - r0), dtype=np.float64)  # column-major panel piece, one row of `pad` per column
+		if mine is not None:
+			pad[: hi - lo] = mine[r0:r1].T
+		allp = comm.all_gather(pad.reshape(-1)).reshape(comm.size, per, r1 - r0)
+		for r in range(comm.size):
+			a, b = probe_range(m, r, comm.size)
+			if b > a:
+				out[r0:r1, a:b] = allp[r, : b - a].T
+	return out

@@ -121,6 +121,15 @@ est = MeanEstimator(covariance=True)
 cc = CountCriterion(100)
 used = trace._run_batched(sampler, est, cc, 24, lambda r: None, EstimatorResult(est, cc), comm, 32)
 out["batched"] = [used, len(est), est.estimate]
+# (5) block drivers: columns of a block product split over the ranks, panels all-gathered
+rng = np.random.default_rng(0)
+B = rng.standard_normal((40, 40)); B = B + B.T
+X = rng.standard_normal((40, 7))
+Y = sharding.sharded_columns(lambda Z: B @ Z, X, comm, chunk_bytes=256)  # several pieces
+q = sharding.sharded_columns(lambda Z: np.einsum("ij,ij->j", Z, B @ Z)[None, :], X, comm).ravel()
+y1 = sharding.sharded_columns(lambda Z: B @ Z, X[:, :1], comm)  # a single column is not split
+out["block"] = [float(np.abs(Y - B @ X).max()), float(np.abs(q - np.einsum("ij,ij->j", X, B @ X)).max()),
+                float(np.abs(y1 - B @ X[:, :1]).max()), float(Y.sum()), float(q.sum())]
 print("RESULT " + json.dumps(out), flush=True)
 dist.destroy_process_group()
 """
@@ -154,6 +163,7 @@ def test_gloo_world2_sharded_driver_matches_single_process(golden, tmp_path):
 		outs.append(json.loads([ln for ln in o.splitlines() if ln.startswith("RESULT ")][-1][7:]))
 	assert outs[0]["fixed_records"] == outs[1]["fixed_records"] and outs[0]["adaptive"] == outs[1]["adaptive"]
 	assert outs[0]["fixed_owned"] == [0, 100] and outs[1]["fixed_owned"][0] == 100
+	assert max(outs[0]["block"][:3]) < 1e-12 and outs[0]["block"] == outs[1]["block"]  # identical bytes on both ranks
 
 	S = golden["hutch_log_count200_seed5_full_b32_samples"]
 	S = np.concatenate([S, S[::-1] * 1.01, S * 0.99])
