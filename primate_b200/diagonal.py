@@ -6,8 +6,8 @@ import numpy as np
 import scipy as sp
 
 from .estimators import ConvergenceCriterion, EstimatorResult, MeanEstimator, convergence_criterion
-from .operators import is_valid_operator
-from .random import isotropic
+from .operators import MatrixFunction, is_valid_operator
+from .random import ProbeStream, isotropic
 
 
 def diag(
@@ -53,6 +53,8 @@ def xdiag(A: np.ndarray, m: Optional[int] = None, pdf: str = "sphere", seed: Uni
 	(diagonal.py:99-138)."""
 	m = 2 * A.shape[0] if m is None else min(m + (m % 2), 2 * A.shape[0])
 	n, m = A.shape[0], m // 2
+	if isinstance(A, MatrixFunction) and isinstance(pdf, str):
+		return _xdiag_device(A, n, m, pdf, np.random.default_rng(seed=seed))
 
 	def dprod(X, Y):  # diag(X Y^T) of two (n, m) panels, as a column
 		return np.einsum("ij,ij->i", X, Y)[:, np.newaxis]
@@ -80,3 +82,41 @@ def xdiag(A: np.ndarray, m: Optional[int] = None, pdf: str = "sphere", seed: Uni
 
 	d = dQZ + (-dQSSZ + dNY - dNTQ + dNQSST) / m
 	return d.ravel()
+
+
+def _xdiag_device(A: MatrixFunction, n: int, m: int, pdf: str, rng: np.random.Generator) -> np.ndarray:
+	"""XDiag with every n x m panel resident on the GPU: the same formulas as above on the same probes (device generator
+	for Rademacher probes, host generator + one upload otherwise), block products from the Lanczos engine (columns split
+	over the ranks when the MatrixFunction has a `comm`), thin QR / small inverses from torch on the same device."""
+	import torch
+
+	from . import engine
+
+	stream = ProbeStream(n, pdf, seed=rng, dtype=A.dtype)
+	cols, off = [], 0
+	for k in engine.block_sizes(m, 64):
+		cols.append(stream.block(k, off))
+		off += k
+	Nw = torch.cat(cols, dim=1) if len(cols) > 1 else cols[0]
+	stream.finish(m)
+	del cols
+
+	Y = A.matmat_device(Nw)
+	Q, R = torch.linalg.qr(Y, mode="reduced")
+	dNY = (Nw * Y).sum(dim=1)
+	del Y
+
+	Z = A.matmat_device(Q)  # A.T @ Q: a matrix function of a symmetric operator is its own transpose
+	T = Z.T @ Nw
+	R_inv = torch.linalg.inv(R)
+	S = R_inv.T / torch.linalg.norm(R_inv, dim=1)
+	QS = Q @ S
+
+	dQZ = (Q * Z).sum(dim=1)
+	dQSSZ = (QS * (Z @ S)).sum(dim=1)
+	dNTQ = (Nw * (Q @ T)).sum(dim=1)
+	dST = (S * T).sum(dim=0)
+	dNQSST = (Nw * (QS * dST[None, :])).sum(dim=1)
+
+	d = dQZ + (-dQSSZ + dNY - dNTQ + dNQSST) / m
+	return d.double().cpu().numpy().ravel()

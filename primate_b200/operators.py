@@ -168,6 +168,45 @@ class MatrixFunction(LinearOperator):
 		                                        coeffs.data_ptr(), out["xnorm2"].data_ptr(), Y.data_ptr(), engine._stream_ptr()))  # fmt: skip
 		return self.device_op._from_internal(Y)  # the basis was combined in the operator's row order
 
+	# ---- device-panel API (block drivers that keep their panels on the GPU) -----------------------------------------
+	def _split_columns(self, m: int):
+		c = self._comm
+		if c.size > 1 and m > 1 and c.backend == "nccl":
+			lo, hi = sharding.probe_range(m, c.rank, c.size)
+			return c, lo, hi, -(-m // c.size)
+		return None, 0, m, m
+
+	def matmat_device(self, Xd):
+		"""f(A) X for a device panel Xd (n, m), row-major, left intact -> device panel (n, m).  With `comm` set, every
+		rank runs its own column range and the panels are all-gathered over NCCL."""
+		torch = engine._torch()
+		n, m = int(Xd.shape[0]), int(Xd.shape[1])
+		c, lo, hi, per = self._split_columns(m)
+		mine = torch.zeros((n, per), dtype=Xd.dtype, device=Xd.device) if c is not None else torch.empty_like(Xd)
+		kmax = 8 if self._deg * n * 8 * 8 > (8 << 30) else 32  # bound the stored basis (deg x n x k)
+		done = lo
+		for kb in engine.block_sizes(hi - lo, kmax):
+			mine[:, done - lo : done - lo + kb] = self.matmat_block(_block_copy(Xd, done, kb))
+			done += kb
+		if c is None:
+			return mine
+		allp = c.all_gather_tensor(mine)  # (size, n, per): rank r holds the global columns [r per, r per + per)
+		return allp.permute(1, 0, 2).reshape(n, c.size * per)[:, :m].contiguous()
+
+	def quad_device(self, Xd):
+		"""x^T f(A) x for every column of the device panel Xd (n, m) (left intact) -> device tensor (m,) float64."""
+		torch = engine._torch()
+		m = int(Xd.shape[1])
+		c, lo, hi, per = self._split_columns(m)
+		mine = torch.zeros(per if c is not None else m, dtype=torch.float64, device=Xd.device)
+		done = lo
+		for kb in engine.block_sizes(hi - lo, 64):
+			mine[done - lo : done - lo + kb] = self.quad_block(_block_copy(Xd, done, kb))
+			done += kb
+		if c is None:
+			return mine
+		return c.all_gather_tensor(mine).reshape(-1)[:m].contiguous()
+
 	# ---- host-array API of the reference ------------------------------------------------------------------------
 	def _matvec(self, x: np.ndarray):
 		r"""Estimates $x \mapsto f(A) x$ with a degree-`deg` Krylov expansion (operators.py:102-124)."""
@@ -262,6 +301,12 @@ class MatrixFunction(LinearOperator):
 			self._alpha[:] = last["alpha"][-1].cpu().numpy()
 			self._beta[:] = last["beta"][-1].cpu().numpy()
 		return y
+
+
+def _block_copy(Xd, first: int, k: int):
+	"""Columns [first, first + k) of a row-major device panel as a fresh contiguous probe block (the engine clobbers it)."""
+	B = Xd[:, first : first + k]
+	return B.clone() if B.is_contiguous() else B.contiguous()
 
 
 def _offsets(sizes):

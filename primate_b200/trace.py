@@ -248,12 +248,16 @@ def hutchpp(
 	f_dtype = is_valid_operator(A)
 	N: int = A.shape[0]
 	rng = np.random.default_rng(seed)
-	draw = isotropic(pdf=pdf, seed=rng)
 	if np.prod(A.shape) == 0:
 		return 0.0 if not full else (0.0, EstimatorResult())
 
 	nb = (N // 3) if m is None else m
 	nb += nb % 3
+	if isinstance(A, MatrixFunction) and isinstance(pdf, str) and mode in ("reduced", "full"):
+		stream = ProbeStream(N, pdf, seed=rng, dtype=f_dtype)
+		if stream.on_device:
+			return _hutchpp_device(A, nb, mode, stream, full)
+	draw = isotropic(pdf=pdf, seed=rng)
 
 	## range sketch
 	WB = draw(size=(N, nb)).astype(f_dtype)
@@ -273,6 +277,45 @@ def hutchpp(
 	result.estimate = tr_rng + tr_defl
 	result.nit = 2 * nb
 	result.samples = np.concatenate([np.ravel(rng_ests), defl_ests])
+	return result.estimate, result
+
+
+def _hutchpp_device(A: MatrixFunction, nb: int, mode: str, stream: ProbeStream, full: bool):
+	"""Hutch++ with every panel resident on the GPU (same estimator, same probes as the host path above): the probes
+	come from the device generator (the columns `isotropic` would draw, in order), the block products and quadratic
+	forms from the Lanczos engine (columns split over the ranks when the MatrixFunction has a `comm`), and the thin QR /
+	projection -- library algebra in the reference too (np.linalg.qr) -- from torch on the same device."""
+	import torch
+
+	from . import engine
+
+	def draw(first: int, count: int):
+		cols, off = [], 0
+		for k in engine.block_sizes(count, 64):
+			cols.append(stream.block(k, first + off))
+			off += k
+		return torch.cat(cols, dim=1) if len(cols) > 1 else cols[0]
+
+	## range sketch
+	WB = draw(0, nb)
+	Q = torch.linalg.qr(A.matmat_device(WB), mode="reduced")[0]
+	del WB
+	rng_ests = (A.matmat_device(Q) * Q).sum(dim=0) if mode == "full" else A.quad_device(Q)
+	tr_rng = float(rng_ests.sum().item())
+
+	## Hutchinson on the complement of range(Q)
+	G = draw(nb, nb)
+	G -= Q @ (Q.T @ G)
+	defl_ests = (A.matmat_device(G) * G).sum(dim=0)
+	tr_defl = float(defl_ests.sum().item()) / nb
+	stream.finish(2 * nb)
+
+	if not full:
+		return tr_rng + tr_defl
+	result = EstimatorResult()
+	result.estimate = tr_rng + tr_defl
+	result.nit = 2 * nb
+	result.samples = np.concatenate([rng_ests.double().cpu().numpy().ravel(), defl_ests.double().cpu().numpy().ravel()])
 	return result.estimate, result
 
 

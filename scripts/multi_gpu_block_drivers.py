@@ -1,4 +1,4 @@
-"""Block drivers on several GPUs: `hutchpp`, `xdiag` and `M @ block` on a MatrixFunction built with
+"""Block drivers on several GPUs: `hutchpp`, `xdiag` (panels resident on the GPUs), `M @ block` (host panels) and `M.matmat_device` on a MatrixFunction built with
 comm="auto" (columns of every block product split over the ranks, panels all-gathered over NCCL) against the same calls
 on one GPU.  Launch:
 
@@ -30,7 +30,7 @@ def main():
 	ap.add_argument("--grid", type=int, default=96)
 	ap.add_argument("--deg", type=int, default=80)
 	ap.add_argument("--m", type=int, default=64)
-	ap.add_argument("--only", default="matmat,xdiag,hutchpp")
+	ap.add_argument("--only", default="matmat,matmat_device,xdiag,hutchpp")
 	ap.add_argument("--out", default="gpurun_out/block_drivers.json")
 	args = ap.parse_args()
 
@@ -65,8 +65,10 @@ def main():
 	X = np.random.default_rng(5).standard_normal((n, args.m))
 	rec = {"n": n, "nnz": int(A.nnz), "deg": args.deg, "m": args.m, "world": world}
 	names = args.only.split(",")
+	Xd = torch.from_numpy(X).cuda()
 	for name, call in (
 		("matmat", lambda M: M @ X),
+		("matmat_device", lambda M: M.matmat_device(Xd)),
 		("xdiag", lambda M: xdiag(M, m=args.m, pdf="rademacher", seed=2)),
 		("hutchpp", lambda M: np.array([hutchpp(M, m=96, seed=1)])),
 	):
@@ -75,6 +77,7 @@ def main():
 		call(shard)  # warm-up (workspaces, NCCL channels)
 		y1, t1 = timed(lambda: call(solo))
 		yN, tN = timed(lambda: call(shard))
+		y1, yN = [y.cpu().numpy() if hasattr(y, "cpu") else y for y in (y1, yN)]
 		err = float(np.max(np.abs(np.asarray(yN) - np.asarray(y1))) / np.max(np.abs(np.asarray(y1))))
 		# the same bytes on every rank: compare a checksum
 		chk = torch.tensor([float(np.sum(np.asarray(yN, dtype=np.float64)))], dtype=torch.float64, device="cuda")

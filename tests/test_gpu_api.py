@@ -122,6 +122,54 @@ def test_block_drivers_on_matrix_function(golden):
 	assert np.linalg.norm(d - np.diag(expA)) < 0.1 * np.linalg.norm(np.diag(expA))
 
 
+def test_hutchpp_device_panels_match_host_algebra(golden):
+	"""hutch++ on a MatrixFunction keeps its panels on the GPU (device probes, device thin QR); the same call on the
+	operator wrapped as a plain LinearOperator runs the reference's host algebra on the same probes.  Also the
+	device-panel products themselves, and that the user's Generator ends where the host path leaves it."""
+	import torch
+	from scipy.sparse.linalg import LinearOperator
+
+	from primate_b200.operators import MatrixFunction
+	from primate_b200.trace import hutchpp
+
+	A = _L30(golden)
+	n = A.shape[0]
+	M = MatrixFunction(A, "exp", deg=30, orth=30, t=-0.3)
+	X = np.random.default_rng(4).standard_normal((n, 37))
+	Xd = torch.from_numpy(X).cuda()
+	assert np.allclose(M.matmat_device(Xd).cpu().numpy(), M @ X, rtol=1e-11, atol=1e-11)
+	assert np.allclose(M.quad_device(Xd).cpu().numpy(), M.quad(X), rtol=1e-11)
+	assert np.array_equal(Xd.cpu().numpy(), X)  # panels are left intact
+	for m in (30, 64):
+		g1, g2 = np.random.default_rng(9), np.random.default_rng(9)
+		dev, info = hutchpp(M, m=m, mode="full", seed=g1, full=True)
+		plain = LinearOperator(M.shape, matvec=M._matvec, matmat=M._matmat, dtype=M.dtype)  # not a MatrixFunction: host algebra
+		host, hinfo = hutchpp(plain, m=m, mode="full", seed=g2, full=True)
+		assert abs(dev / host - 1) < 1e-9 and info.nit == hinfo.nit
+		assert np.allclose(info.samples, hinfo.samples, rtol=1e-6, atol=1e-8 * abs(host))
+		assert g1.integers(1 << 30) == g2.integers(1 << 30)
+	red = hutchpp(M, m=64, seed=9)  # default mode: Lanczos quadrature for the sketched part
+	assert abs(red / host - 1) < 1e-3
+
+
+@pytest.mark.parametrize("pdf", ["rademacher", "sphere"])
+def test_xdiag_device_panels_match_host_algebra(golden, pdf):
+	"""xdiag on a MatrixFunction (panels on the GPU) against the reference's host algebra on the same probes."""
+	from scipy.sparse.linalg import LinearOperator
+
+	from primate_b200.diagonal import xdiag
+	from primate_b200.operators import MatrixFunction
+
+	A = _L30(golden)
+	M = MatrixFunction(A, "exp", deg=30, orth=30, t=-0.3)
+	plain = LinearOperator(M.shape, matvec=M._matvec, matmat=M._matmat, rmatvec=M._matvec, rmatmat=M._matmat, dtype=M.dtype)
+	for m in (20, 100):
+		d_dev = xdiag(M, m=m, pdf=pdf, seed=11)
+		d_host = xdiag(plain, m=m, pdf=pdf, seed=11)
+		assert d_dev.shape == d_host.shape == (A.shape[0],)
+		assert np.max(np.abs(d_dev - d_host)) < 1e-9 * np.max(np.abs(d_host))
+
+
 @pytest.fixture(scope="module")
 def c2():
 	A = laplacian_2d(1000)
