@@ -169,6 +169,14 @@ class MatrixFunction(LinearOperator):
 		return self.device_op._from_internal(Y)  # the basis was combined in the operator's row order
 
 	# ---- device-panel API (block drivers that keep their panels on the GPU) -----------------------------------------
+	def _basis_block_width(self, n: int, budget: int = 40 << 30) -> int:
+		"""Widest probe block (power of two <= 32) whose stored Lanczos basis (deg x n x k) stays within `budget` bytes."""
+		per_column = self._deg * n * np.dtype(self.dtype).itemsize
+		k = 32
+		while k > 1 and k * per_column > budget:
+			k >>= 1
+		return k
+
 	def _split_columns(self, m: int):
 		c = self._comm
 		if c.size > 1 and m > 1 and c.backend == "nccl":
@@ -183,7 +191,7 @@ class MatrixFunction(LinearOperator):
 		n, m = int(Xd.shape[0]), int(Xd.shape[1])
 		c, lo, hi, per = self._split_columns(m)
 		mine = torch.zeros((n, per), dtype=Xd.dtype, device=Xd.device) if c is not None else torch.empty_like(Xd)
-		kmax = 8 if self._deg * n * 8 * 8 > (8 << 30) else 32  # bound the stored basis (deg x n x k)
+		kmax = self._basis_block_width(n)
 		done = lo
 		for kb in engine.block_sizes(hi - lo, kmax):
 			mine[:, done - lo : done - lo + kb] = self.matmat_block(_block_copy(Xd, done, kb))
@@ -274,7 +282,7 @@ class MatrixFunction(LinearOperator):
 
 		n, m = X.shape
 		Yt = torch.empty((m, n), dtype=engine._tdtype(self.dtype), device="cuda")  # columns: an F-ordered (n, m) host array
-		kmax = 8 if self._deg * n * 8 * 8 > (8 << 30) else 32  # bound the stored basis (deg x n x k)
+		kmax = self._basis_block_width(n)
 		for done, kb, B in self._device_blocks(X, kmax):
 			Y = self.matmat_block(B)
 			_ffi.check(_ffi.lib().slq_block_to_columns(Y.data_ptr(), n, kb, self.device_op.code, Yt[done : done + kb].data_ptr(),
