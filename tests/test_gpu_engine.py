@@ -193,6 +193,39 @@ def test_spmm_power_law_graph_laplacian(eng, dtype, k):
 		assert np.max(np.abs(Y2 - ref) / scale) < (1e-13 if dtype == np.float64 else 2e-5)
 
 
+def test_auto_order_balances_power_law_rows(eng):
+	"""`reorder="auto"` on a large operator with hub rows picks the row-balancing order (every 120-row tile then holds
+	about the same number of non-zeros); SpMM and Lanczos coefficients are those of the caller's order."""
+	rng = np.random.default_rng(3)
+	n = 70001
+	w = 1.0 / np.arange(1, n + 1) ** 0.95
+	src = rng.choice(n, size=700000, p=w / w.sum())
+	dst = rng.integers(0, n, size=700000)
+	keep = src != dst
+	W = sp.coo_matrix((np.ones(keep.sum()), (src[keep], dst[keep])), shape=(n, n)).tocsr()
+	W = ((W + W.T) > 0).astype(np.float64)
+	L = (sp.diags(np.asarray(W.sum(axis=1)).ravel()) - W).tocsr()
+	L.sort_indices()
+	deg = np.diff(L.indptr)
+	assert deg.max() > max(1024, 64 * L.nnz // n)
+	op = eng.DeviceOperator(L)  # reorder="auto"
+	perm = op.perm.cpu().numpy()
+	assert np.array_equal(np.sort(perm), np.arange(n))
+	per_tile = np.add.reduceat(deg[perm], np.arange(0, n, 120))[:-1]
+	nat_tile = np.add.reduceat(deg, np.arange(0, n, 120))[:-1]
+	assert per_tile.max() - np.median(per_tile) <= deg.max() and nat_tile.max() > 3 * per_tile.max() - 2 * deg.max()
+	X = rng.standard_normal((n, 32))
+	Y = op.matmat(eng.block_from_columns(X, np.float64)).cpu().numpy()
+	scale = np.abs(L) @ np.abs(X) + 1.0
+	assert np.max(np.abs(Y - L @ X) / scale) < 1e-13
+	nat = eng.DeviceOperator(L, reorder=False)
+	assert nat.perm is None
+	o1 = op.lanczos(eng.block_from_columns(X, np.float64), 10, 1e-8, 0, 2)
+	o2 = nat.lanczos(eng.block_from_columns(X, np.float64), 10, 1e-8, 0, 2)
+	assert rel_err(o1["alpha"].cpu().numpy()[:, :10], o2["alpha"].cpu().numpy()[:, :10]) < 1e-10
+	assert rel_err(o1["beta"].cpu().numpy()[:, 1:10], o2["beta"].cpu().numpy()[:, 1:10]) < 1e-10
+
+
 @pytest.mark.parametrize("k", [16, 32, 64])
 def test_lanczos_ragged_vs_oracle(eng, oracle, k):
 	"""alpha/beta of the blocked device Lanczos on the ragged matrix against the compiled reference, per probe."""
