@@ -41,6 +41,7 @@ def _code(np_dtype) -> int:
 	raise TypeError("Only 32- or 64-bit floats are supported.")  # mirrors the pybind11 overload failure
 
 
+REORDER_GRID = 148  # CTAs of the persistent step-A grid (SMs of a B200)
 REORDER_TILE = 120  # rows per cluster: the row tile of the step-A kernel at k = 32 fp64 (slq_stepa_tma.cuh)
 REORDER_MIN_ROWS = 1 << 16  # below this every probe block fits in L2/L1 anyway
 
@@ -59,6 +60,35 @@ def _want_reorder(reorder, n: int, nnz: int) -> bool:
 	return bool(reorder)
 
 
+def _balance_tiles(weights: np.ndarray, ncta: int) -> np.ndarray:
+	"""Tile placement for a persistent grid: returns `place` with place[j] = the tile to put at position j, where
+	position j is processed by CTA j % ncta.  Longest-processing-time greedy with the per-CTA tile counts fixed (heaviest
+	tile to the least loaded CTA that still has a free position); each CTA runs its tiles heaviest first.  The last
+	tile keeps its position (it may be short of rows)."""
+	import heapq
+
+	nt = len(weights)
+	if nt < 2 * ncta:
+		return np.arange(nt)
+	cap = [len(range(c, nt - 1, ncta)) for c in range(ncta)]  # free positions per CTA, the last position excluded
+	load = [0] * ncta
+	load[(nt - 1) % ncta] = int(weights[nt - 1])
+	heap = [(load[c], c) for c in range(ncta) if cap[c] > 0]
+	heapq.heapify(heap)
+	got = [[] for _ in range(ncta)]
+	for t in np.argsort(-weights[: nt - 1], kind="stable"):
+		ld, c = heapq.heappop(heap)
+		got[c].append(int(t))
+		cap[c] -= 1
+		if cap[c] > 0:
+			heapq.heappush(heap, (ld + int(weights[t]), c))
+	place = np.empty(nt, dtype=np.int64)
+	place[nt - 1] = nt - 1
+	for c in range(ncta):
+		place[c : nt - 1 : ncta] = got[c]
+	return place
+
+
 def _balance_rows_device(rowptr, colidx, vals, n: int, tile: int):
 	"""P A P^T with the rows dealt round-robin to the row tiles by decreasing length, so that every tile (hence every
 	persistent CTA of the step-A kernel) carries about the same number of non-zeros.  Device tensors in and out
@@ -70,7 +100,12 @@ def _balance_rows_device(rowptr, colidx, vals, n: int, tile: int):
 	order = torch.argsort(deg, descending=True, stable=True)
 	ntiles = -(-n // tile)
 	pad = torch.full((ntiles * tile - n,), -1, dtype=torch.int64, device=dev)
-	grid = torch.cat([order, pad]).reshape(tile, ntiles).t().reshape(-1)  # rank r -> tile r % ntiles, slot r // ntiles
+	grid = torch.cat([order, pad]).reshape(tile, ntiles)  # rank r -> slot r // ntiles of tile r % ntiles
+	# Tile t is processed by persistent CTA t % 148.  The tiles are equal but for their one hub row, and the top hubs
+	# alone are ~10% of a CTA's non-zeros on an R-MAT graph: place the tiles so that every CTA gets the same total.
+	weights = torch.where(grid >= 0, deg[grid.clamp(min=0)], torch.zeros_like(grid)).sum(dim=0)
+	place = torch.from_numpy(_balance_tiles(weights.cpu().numpy(), REORDER_GRID)).to(dev)
+	grid = grid[:, place].t().reshape(-1)
 	perm = grid[grid >= 0]
 	inv = torch.empty(n, dtype=torch.int64, device=dev)
 	inv[perm] = torch.arange(n, device=dev)
