@@ -54,6 +54,9 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src, uint32
 #ifndef SLQ_TMA_U
 #define SLQ_TMA_U 5  // gathers per row per round
 #endif
+#ifndef SLQ_TMA_HOIST
+#define SLQ_TMA_HOIST 1  // per-column scales in registers: 0 none, 1 beta*scale_p (+1% on C2), 2 both (spills at 128 registers: -17%)
+#endif
 #ifndef SLQ_TMA_UB
 #define SLQ_TMA_UB 8  // gathers in flight per thread, non-zero-balanced variant
 #endif
@@ -321,6 +324,15 @@ __global__ void __launch_bounds__(TmaTiling<T, K, LONGROWS>::NTHREADS, 1)
     const int slot = sub * V;
     int stage = 0;
     uint32_t phase = 0;
+    // this thread's probe columns never change: keep their scales in registers (the per-row shared-memory reads were
+    // a fifth of the kernel's L1/shared-memory wavefronts, and that pipe is the co-bottleneck next to HBM)
+    constexpr int HOIST = sizeof(T) == 8 ? SLQ_TMA_HOIST : 0;  // the fp32 k = 64 variant has no registers to spare
+    T rc_r[V], brp_r[V];
+#pragma unroll
+    for (int q = 0; q < V; ++q) {
+      rc_r[q] = (PLAIN || HOIST < 2) ? (T)1 : s_rc[slot + q];
+      brp_r[q] = (PLAIN || HOIST < 1) ? (T)0 : s_brp[slot + q];
+    }
     if constexpr (!LONGROWS) {
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
       const int row0 = tile * TILE;
@@ -377,8 +389,9 @@ __global__ void __launch_bounds__(TmaTiling<T, K, LONGROWS>::NTHREADS, 1)
                   const Pack<T, V> qcr = *reinterpret_cast<const Pack<T, V>*>(s_uc + (size_t)rl * K + slot);
 #pragma unroll
                   for (int q = 0; q < V; ++q) {
-                    const T rcq = s_rc[slot + q];
-                    wv.v[q] = FIRST ? a2[r][q] * rcq : a2[r][q] * rcq - s_brp[slot + q] * pv.v[q];
+                    const T rcq = HOIST >= 2 ? rc_r[q] : s_rc[slot + q];
+                    const T brq = HOIST >= 1 ? brp_r[q] : s_brp[slot + q];
+                    wv.v[q] = FIRST ? a2[r][q] * rcq : a2[r][q] * rcq - brq * pv.v[q];
                     acc_a[q] += (double)(qcr.v[q] * rcq) * (double)wv.v[q];
                   }
                   st_pack<T, V, false>(w + off, wv);
@@ -510,8 +523,9 @@ __global__ void __launch_bounds__(TmaTiling<T, K, LONGROWS>::NTHREADS, 1)
                 const Pack<T, V> qcr = *reinterpret_cast<const Pack<T, V>*>(s_uc + (size_t)rl * K + slot);
 #pragma unroll
                 for (int q = 0; q < V; ++q) {
-                  const T rcq = s_rc[slot + q];
-                  wv.v[q] = FIRST ? av.v[q] * rcq : av.v[q] * rcq - s_brp[slot + q] * pv.v[q];
+                  const T rcq = HOIST >= 2 ? rc_r[q] : s_rc[slot + q];
+                  const T brq = HOIST >= 1 ? brp_r[q] : s_brp[slot + q];
+                  wv.v[q] = FIRST ? av.v[q] * rcq : av.v[q] * rcq - brq * pv.v[q];
                   acc_a[q] += (double)(qcr.v[q] * rcq) * (double)wv.v[q];
                 }
                 st_pack<T, V, false>(w + off, wv);
