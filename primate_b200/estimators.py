@@ -3,8 +3,7 @@
 Host-side and scalar-only, exactly as in the reference: the device hands over per-probe quadrature values (or a
 pre-reduced (count, mean, M2) record, see `MeanEstimator.merge`) and the criteria decide when to stop.
 """
-from dataclasses import dataclass, field
-from operator import and_, not_, or_
+import operator
 from typing import Callable, Iterable, Literal, Optional, Protocol, Sized, Union, runtime_checkable
 
 import numpy as np
@@ -48,20 +47,25 @@ class Estimator(Sized, Protocol):
 
 
 class ConvergenceCriterion:
-	"""Lazily evaluated predicate on an estimator; composes with `|`, `&`, `~`."""
+	"""Lazily evaluated predicate on an estimator; composes with `|`, `&`, `~` (each composition is a new criterion
+	that evaluates its parts on the estimator it is called with)."""
 
 	def __init__(self, operation: Callable):
 		assert callable(operation)
 		self._operation = operation
 
+	@staticmethod
+	def _compose(op: Callable, *parts: "ConvergenceCriterion") -> "ConvergenceCriterion":
+		return ConvergenceCriterion(lambda est: op(*(part(est) for part in parts)))
+
 	def __or__(self, other: "ConvergenceCriterion"):
-		return ConvergenceCriterion(lambda est: or_(self(est), other(est)))
+		return self._compose(operator.or_, self, other)
 
 	def __and__(self, other: "ConvergenceCriterion"):
-		return ConvergenceCriterion(lambda est: and_(self(est), other(est)))
+		return self._compose(operator.and_, self, other)
 
 	def __invert__(self):
-		return ConvergenceCriterion(lambda est: not_(self(est)))
+		return self._compose(operator.not_, self)
 
 	def __call__(self, est: Estimator) -> bool:
 		return self._operation(est)
@@ -70,19 +74,22 @@ class ConvergenceCriterion:
 		return "Composite convergence criterion"
 
 
-@dataclass
 class EstimatorResult:
-	"""What `full=True` returns and what callbacks receive."""
+	"""What `full=True` returns and what callbacks receive: the estimator, the stopping criterion, the current
+	estimate, a status message, the number of iterations and a free-form `info` dict (unpacks in that order)."""
 
-	estimator: Optional[Estimator] = None
-	criterion: Union[ConvergenceCriterion, str, None] = None
-	estimate: Union[float, np.ndarray] = 0.0
-	message: str = ""
-	nit: int = 0
-	info: dict = field(default_factory=dict)
+	_FIELDS = ("estimator", "criterion", "estimate", "message", "nit", "info")
+
+	def __init__(self, estimator: Optional[Estimator] = None, criterion: Union[ConvergenceCriterion, str, None] = None,
+	             estimate: Union[float, np.ndarray] = 0.0, message: str = "", nit: int = 0, info: Optional[dict] = None):  # fmt: skip
+		self.estimator, self.criterion, self.estimate = estimator, criterion, estimate
+		self.message, self.nit, self.info = message, nit, ({} if info is None else info)
 
 	def __iter__(self) -> Iterable:
-		return iter((self.estimator, self.criterion, self.estimate, self.message, self.nit, self.info))
+		return (getattr(self, name) for name in self._FIELDS)
+
+	def __repr__(self) -> str:
+		return "EstimatorResult(" + ", ".join(f"{name}={getattr(self, name)!r}" for name in self._FIELDS) + ")"
 
 
 class MeanEstimator(Estimator):
