@@ -193,6 +193,39 @@ def test_spmm_power_law_graph_laplacian(eng, dtype, k):
 		assert np.max(np.abs(Y2 - ref) / scale) < (1e-13 if dtype == np.float64 else 2e-5)
 
 
+@pytest.mark.parametrize("seed", range(8))
+def test_spmm_irregular_random_shapes(eng, seed):
+	"""Randomised shapes for the non-zero-balanced step-A variant: sizes around the 120-row tile and the chunk capacity,
+	hubs in the first, a middle and the last (partial) tile, empty rows, every block width and both precisions; SpMM
+	and three Lanczos steps (alpha through the fused epilogue) against SciPy / the natural-order operator."""
+	rng = np.random.default_rng(100 + seed)
+	n = int(rng.choice([97, 121, 240, 1000, 2399, 4097, 7919]))
+	k = int(rng.choice([8, 16, 32, 64]))
+	dtype = np.float64 if seed % 2 == 0 else np.float32
+	base = sp.random(n, n, density=min(0.5, 4.0 / n), random_state=int(rng.integers(1 << 30)), format="lil")
+	for hub in {0, n // 2, n - 1}:  # rows far longer than 64 non-zeros, up to completely full
+		cols = rng.choice(n, size=int(rng.integers(min(n, 70), n + 1)), replace=False)
+		base[hub, cols] = rng.standard_normal(len(cols))
+	A = base.tocsr()
+	A = (A + A.T).tocsr().astype(dtype)
+	A.sort_indices()
+	assert np.diff(A.indptr).max() > 64
+	X = rng.standard_normal((n, k)).astype(dtype)
+	ref = A.astype(np.float64) @ X.astype(np.float64)
+	scale = np.abs(A.astype(np.float64)) @ np.abs(X.astype(np.float64)) + 1.0
+	tol = 1e-13 if dtype == np.float64 else 2e-5
+	ops = [eng.DeviceOperator(A, dtype=dtype, reorder=r) for r in (False, "balance")]
+	for op in ops:
+		Y = op.matmat(eng.block_from_columns(X, dtype)).cpu().numpy()
+		assert np.max(np.abs(Y - ref) / scale) < tol
+	outs = [op.lanczos(eng.block_from_columns(X, dtype), 3, 1e-8, 0, 2) for op in ops]
+	a0, a1 = (o["alpha"].cpu().numpy()[:, :3] for o in outs)
+	assert rel_err(a1, a0) < (1e-10 if dtype == np.float64 else 1e-3)
+	# alpha_1 = x^T A x / x^T x per probe
+	want = np.einsum("ij,ij->j", X.astype(np.float64), ref) / np.einsum("ij,ij->j", X.astype(np.float64), X.astype(np.float64))
+	assert np.max(np.abs(a0[:, 0] - want)) < (1e-10 if dtype == np.float64 else 1e-3) * max(1.0, np.max(np.abs(want)))
+
+
 def test_auto_order_balances_power_law_rows(eng):
 	"""`reorder="auto"` on a large operator with hub rows picks the row-balancing order (every 120-row tile then holds
 	about the same number of non-zeros); SpMM and Lanczos coefficients are those of the caller's order."""
