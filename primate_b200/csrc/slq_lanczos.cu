@@ -13,6 +13,8 @@
 // Grid-wide reductions (alpha, beta, MGS coefficients) are deterministic: per-CTA partials in a table, summed
 // in fixed order by the last CTA to finish, which also runs the scalar recurrence bookkeeping (early break
 // mask, lanczos.h:140).  Dots and norms accumulate in fp64 for both fp32 and fp64 panels.
+#include <cooperative_groups.h>
+
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
@@ -521,6 +523,145 @@ __global__ void __launch_bounds__(NT) k_axpy(int64_t n, T* __restrict__ v, const
   }
 }
 
+// ---- kernel "re-orthogonalisation chain": the whole modified-Gram-Schmidt sweep of one Lanczos step ------------
+// The k_axpy chain above costs one launch per visited basis vector, and at small n (an 8 MB panel at n = 32 768)
+// each of them is launch-latency-bound (profiles/r01f_ncu_c4_reorth_launches.txt).  When the panel of v fits in the
+// shared memory of one CTA per SM, this cooperative kernel keeps every CTA's slice of v on chip for the whole sweep:
+//   pass m : v -= coef_{m-1} u_{m-1};  partial dots <u_m,u_m>, <v,u_m>  ->  grid barrier  ->  every CTA sums the
+//            per-CTA table in the same fixed order and forms coef_m (the FIN_COEF arithmetic, lanczos.h:59-64);
+//   end    : v -= coef_last u_last, v is written back once, ||v||^2 partials, last CTA records beta (FIN_BETA).
+// HBM traffic per visited vector drops from (read v, u_{m-1}, u_m + write v) to one read of u_m (u_{m-1} is an L2
+// hit), and the per-vector cost from a launch to a grid barrier.  The partial tables alternate between two buffers
+// so that a CTA already in pass m+1 never overwrites a table a slower CTA is still summing.
+constexpr int CHAIN_MAX_VISIT = 1024;
+struct ChainVisit {
+  int count;
+  uint16_t panel[CHAIN_MAX_VISIT];  // physical panel index of each visited column (0 = caller's X)
+};
+
+template <typename T>
+__device__ __forceinline__ const T* chain_panel(const T* x0, const char* base, size_t panel_bytes, int ph) {
+  return ph == 0 ? x0 : reinterpret_cast<const T*>(base + panel_bytes * (size_t)(ph - 1));
+}
+
+template <typename T, int K>
+__global__ void __launch_bounds__(NT, 1)
+    k_reorth_chain(int64_t n, int64_t chunk /* packs per CTA, multiple of NT */, T* __restrict__ v, const T* x0, const char* base,
+                   size_t panel_bytes, const double* scales, LzScal* sc, double* scale_v, double* partial, StepOut so,
+                   const __grid_constant__ ChainVisit visit) {
+  namespace cg = cooperative_groups;
+  using M = BlockMap<T, K>;
+  constexpr int V = M::V, LPR = M::LPR;
+  constexpr int NS = 2 * K;
+  constexpr int NCH = NT / NS > 0 ? NT / NS : 1;
+  extern __shared__ __align__(32) unsigned char s_dyn[];
+  Pack<T, V>* s_v = reinterpret_cast<Pack<T, V>*>(s_dyn);
+  __shared__ double smem[NT > NWARP * 2 * K ? NT : NWARP * 2 * K];
+  __shared__ double s_coef[MAXK];
+  cg::grid_group grid = cg::this_grid();
+
+  const int t = threadIdx.x;
+  const int slot = (t % LPR) * V;
+  const int64_t nvec = n * LPR;
+  const int64_t e0 = (int64_t)blockIdx.x * chunk;
+  int64_t e1 = e0 + chunk;
+  if (e1 > nvec) e1 = nvec;
+  const int cnt = e1 > e0 ? (int)(e1 - e0) : 0;  // packs of this CTA; local pack l <-> global pack e0 + l
+  const size_t table = (size_t)gridDim.x * NS;
+
+  T cf[V];
+#pragma unroll
+  for (int i = 0; i < V; ++i) cf[i] = (T)sc->coef[slot + i];  // alpha_j r_c, left by FIN_ALPHA
+
+  const T* u_prev = chain_panel<T>(x0, base, panel_bytes, visit.panel[0]);
+  for (int m = 0; m < visit.count; ++m) {
+    const int ph = visit.panel[m];
+    const T* u_cur = chain_panel<T>(x0, base, panel_bytes, ph);
+    double acc[2][V];
+#pragma unroll
+    for (int a = 0; a < 2; ++a)
+#pragma unroll
+      for (int i = 0; i < V; ++i) acc[a][i] = 0.0;
+#pragma unroll 4
+    for (int l = t; l < cnt; l += NT) {
+      const int64_t e = e0 + l;
+      Pack<T, V> vv = (m == 0) ? ld_pack<T, V, LD_STREAM>(v + e * V) : s_v[l];
+      Pack<T, V> a1 = ld_pack<T, V, LD_DEFAULT>(u_prev + e * V);
+      Pack<T, V> a2 = (m == 0) ? a1 : ld_pack<T, V, LD_DEFAULT>(u_cur + e * V);
+#pragma unroll
+      for (int q = 0; q < V; ++q) vv.v[q] = vv.v[q] - cf[q] * a1.v[q];
+      s_v[l] = vv;
+#pragma unroll
+      for (int q = 0; q < V; ++q) {
+        acc[0][q] += (double)a2.v[q] * (double)a2.v[q];
+        acc[1][q] += (double)vv.v[q] * (double)a2.v[q];
+      }
+    }
+    double* tab = partial + (size_t)(m & 1) * table;
+    cta_reduce_slots<K, V, LPR, 2>(acc, tab + (size_t)blockIdx.x * NS, smem);
+    grid.sync();
+    // every CTA: column sums of the table in the order reduce_partials uses (chunks of CTAs, then the chunk sums)
+    {
+      double s = 0.0;
+      if (NS <= NT) {
+        const int col = t % NS, ch = t / NS;
+        if (ch < NCH) {
+          int c = ch;
+          constexpr int U = 10;  // table loads in flight per thread (148 CTAs / NCH = 37 rows per thread at K = 32)
+          for (; c + (U - 1) * NCH < (int)gridDim.x; c += U * NCH) {
+            double p[U];
+#pragma unroll
+            for (int i = 0; i < U; ++i) p[i] = __ldcg(tab + (size_t)(c + i * NCH) * NS + col);
+#pragma unroll
+            for (int i = 0; i < U; ++i) s += p[i];
+          }
+          for (; c < (int)gridDim.x; c += NCH) s += __ldcg(tab + (size_t)c * NS + col);
+        }
+      }
+      __syncthreads();  // cta_reduce_slots' readers are done with smem
+      smem[t] = s;
+      __syncthreads();
+      if (t < K) {
+        double uu = 0.0, vu = 0.0;
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) {
+          uu += smem[c * NS + t];
+          vu += smem[c * NS + K + t];
+        }
+        const double r = scales[(size_t)ph * MAXK + t];
+        const double u_norm = round_to<T>(uu * r * r);
+        const double s_proj = round_to<T>(vu * r);
+        const bool take = (u_norm > so.orth_tol) && (fabs(s_proj) > so.orth_tol);
+        s_coef[t] = take ? round_to<T>(round_to<T>(s_proj / u_norm) * r) : 0.0;
+      }
+      __syncthreads();
+    }
+#pragma unroll
+    for (int i = 0; i < V; ++i) cf[i] = (T)s_coef[slot + i];
+    u_prev = u_cur;
+  }
+
+  // v -= coef_last u_last; write v back; ||v||^2
+  double accn[1][V];
+#pragma unroll
+  for (int i = 0; i < V; ++i) accn[0][i] = 0.0;
+#pragma unroll 4
+  for (int l = t; l < cnt; l += NT) {
+    const int64_t e = e0 + l;
+    Pack<T, V> vv = s_v[l];
+    Pack<T, V> a1 = ld_pack<T, V, LD_DEFAULT>(u_prev + e * V);
+#pragma unroll
+    for (int q = 0; q < V; ++q) vv.v[q] = vv.v[q] - cf[q] * a1.v[q];
+    st_pack<T, V, false>(v + e * V, vv);
+#pragma unroll
+    for (int q = 0; q < V; ++q) accn[0][q] += (double)vv.v[q] * (double)vv.v[q];
+  }
+  __syncthreads();
+  double* tabn = partial + 2 * table;  // a third table: slower CTAs may still be summing either pass table
+  cta_reduce_slots<K, V, LPR, 1>(accn, tabn + (size_t)blockIdx.x * K, smem);
+  if (elect_last_cta(&sc->counter)) finalize<T, K, FIN_BETA>(tabn, sc, scale_v, nullptr, so, smem);
+}
+
 // ---- kernel: export one normalised Lanczos vector block into the caller's basis ----------------------------
 template <typename T, int K>
 __global__ void __launch_bounds__(NT) k_export(int64_t n, const T* __restrict__ u, const double* scale, const LzScal* sc, int m,
@@ -763,6 +904,73 @@ static int op_apply(slq_op* op, const T* X, T* Y, cudaStream_t st) {
   return SLQ_OK;
 }
 
+// SLQ_REORTH=chain|launches forces one of the two re-orthogonalisation paths (A/B timing); default: the chain
+// whenever the panel fits on chip.
+static int reorth_mode() {
+  static int cached = -1;
+  if (cached < 0) {
+    const char* e = getenv("SLQ_REORTH");
+    cached = (e && strcmp(e, "launches") == 0) ? 0 : 1;
+  }
+  return cached;
+}
+
+// Returns 1 when the chain ran, 0 when the caller must take the per-vector launches, < 0 on error.
+template <typename T, int K>
+static int try_reorth_chain(int64_t n, T* v, const T* x0, const Workspace& ws, const std::vector<int>& visit, double* scale_v,
+                            const StepOut& so, cudaStream_t st) {
+  using M = BlockMap<T, K>;
+  if (reorth_mode() == 0 || visit.empty() || (int)visit.size() > CHAIN_MAX_VISIT || ws.npanel + 1 > 65535) return 0;
+  const int sms = sm_count();
+  if (sms <= 0) return 0;
+  const int64_t nvec = n * M::LPR;
+  const int64_t per = (nvec + sms - 1) / sms;
+  int64_t chunk = (per + NT - 1) / NT * NT;
+  if (chunk < NT) chunk = NT;
+  const size_t pack_bytes = sizeof(T) * M::V;
+  const size_t dyn = (size_t)chunk * pack_bytes;
+  // partial tables: two pass tables of grid x 2K doubles and one of grid x K (ws_layout holds 8 * sms x 2 MAXK)
+  static int max_dyn = -1, coop = -1;
+  if (max_dyn < 0) {
+    int dev = 0, optin = 0, c = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+    cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+    cudaDeviceGetAttribute(&c, cudaDevAttrCooperativeLaunch, dev);
+    cudaFuncAttributes fa;
+    if (cudaFuncGetAttributes(&fa, k_reorth_chain<T, K>) != cudaSuccess) return 0;
+    coop = c;
+    max_dyn = optin - (int)fa.sharedSizeBytes - 1024;
+  }
+  if (!coop || (int64_t)dyn > (int64_t)max_dyn) return 0;
+  static size_t occ_checked = (size_t)-1;  // co-residency of the whole grid is what grid.sync() needs
+  static int occ = 0;
+  const int grid = (int)((nvec + chunk - 1) / chunk);  // <= sms
+  static size_t configured = 0;  // per (T, K) instantiation
+  if (dyn > configured) {
+    SLQ_CUDA(cudaFuncSetAttribute(k_reorth_chain<T, K>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_dyn));
+    configured = (size_t)max_dyn;
+  }
+  if (occ_checked != dyn) {
+    SLQ_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_reorth_chain<T, K>, NT, dyn));
+    occ_checked = dyn;
+  }
+  if (occ < 1) return 0;
+  ChainVisit cv;
+  cv.count = (int)visit.size();
+  for (size_t i = 0; i < visit.size(); ++i) cv.panel[i] = (uint16_t)visit[i];
+  int64_t n_ = n, chunk_ = chunk;
+  const char* base = ws.base;
+  size_t panel_bytes = ws.panel_bytes;
+  const double* scales = ws.scales;
+  LzScal* sc = ws.sc;
+  double* partial = ws.partial;
+  StepOut so_ = so;
+  void* args[] = {&n_, &chunk_, &v, &x0, &base, &panel_bytes, &scales, &sc, &scale_v, &partial, &so_, &cv};
+  SLQ_CUDA(cudaLaunchCooperativeKernel((const void*)k_reorth_chain<T, K>, dim3(grid), dim3(NT), args, dyn, st));
+  SLQ_LAUNCH_CHECK();
+  return 1;
+}
+
 template <typename T, int K>
 static int lanczos_impl(slq_op* op, T* X, int deg, double rtol, int orth, int ncv, T* alpha, T* beta, int32_t* steps,
                         double* xnorm2, T* Qout, char* wsbase, cudaStream_t st) {
@@ -842,6 +1050,8 @@ static int lanczos_impl(slq_op* op, T* X, int deg, double rtol, int orth, int nc
       k_axpy<T, K, AX_NORM><<<g_vec, NT, 0, st>>>(n, w, phys[pc], nullptr, ws.sc, scale_of(F), nullptr, ws.partial, so);
       SLQ_LAUNCH_CHECK();
       prof_end(PROF_AXPY, bslot, st);
+    } else if (int ran = try_reorth_chain<T, K>(n, w, X, ws, visit, scale_of(F), so, st); ran != 0) {
+      if (ran < 0) return ran;  // the whole sweep ran as one cooperative kernel (v stays in shared memory)
     } else {
       // visit[0] is always the current column: fuse "v = w - alpha q_c" with the first projection's dots
       k_axpy<T, K, AX_DOT_SAME><<<g_vec, NT, 0, st>>>(n, w, phys[pc], nullptr, ws.sc, nullptr, scale_of(visit[0]), ws.partial, so);

@@ -441,3 +441,40 @@ def test_callback_operator(eng, golden):
 	A, v = golden["A150"], golden["v42"]
 	res = _run_lanczos(eng, aslinearoperator(A), v, 20)
 	assert rel_err(res["alpha"][0, :20], golden["lz_v42_deg20_orth0_a"]) < 1e-10
+
+
+_REORTH_CASE = """
+import sys, numpy as np
+from tests.conftest import laplacian_2d
+from primate_b200 import engine as eng
+g, k, deg, dtype = int(sys.argv[1]), int(sys.argv[2]), int(sys.argv[3]), np.dtype(sys.argv[4]).type
+A = laplacian_2d(g)
+X = eng.block_from_columns(np.random.default_rng(5).standard_normal((g * g, k)).astype(dtype), dtype)
+out = eng.DeviceOperator(A, dtype=dtype).lanczos(X, deg, 1e-8, deg, deg + 1)
+np.savez(sys.argv[5], alpha=out["alpha"].cpu().numpy(), beta=out["beta"].cpu().numpy())
+"""
+
+
+@pytest.mark.parametrize("g,k,dtype,tol", [(200, 64, "float64", 1e-10), (200, 8, "float64", 1e-10), (96, 1, "float64", 1e-10), (160, 64, "float32", 1e-4)])
+def test_reorth_chain_matches_per_vector_launches(eng, oracle, tmp_path, g, k, dtype, tol):
+	"""Full re-orthogonalisation (lanczos.h:52-66) as ONE cooperative kernel per step (v kept in shared memory, a grid
+	barrier per visited vector) against the per-vector launch chain (SLQ_REORTH=launches, separate processes) and,
+	for one probe, against the compiled reference."""
+	import os
+	import subprocess
+	import sys
+
+	root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+	res = {}
+	for mode in ("chain", "launches"):
+		path = str(tmp_path / f"{mode}.npz")
+		env = dict(os.environ, SLQ_REORTH=mode)
+		subprocess.run([sys.executable, "-c", _REORTH_CASE, str(g), str(k), "20", dtype, path], check=True, cwd=root, env=env, timeout=600)
+		res[mode] = np.load(path)
+	assert rel_err(res["chain"]["alpha"][:, :20], res["launches"]["alpha"][:, :20]) < tol
+	assert rel_err(res["chain"]["beta"][:, 1:20], res["launches"]["beta"][:, 1:20]) < tol
+	if dtype == "float64":
+		A = laplacian_2d(g)
+		V = np.random.default_rng(5).standard_normal((g * g, k))
+		ra, rb, _ = oracle.ref_lanczos(A, V[:, k - 1], 20, 1e-8, 20)
+		assert rel_err(res["chain"]["alpha"][k - 1, :20], ra[:20]) < tol and rel_err(res["chain"]["beta"][k - 1, 1:20], rb[1:20]) < tol
