@@ -117,6 +117,21 @@ def test_dense_matmat_tiled_path(eng, k, dtype):
 	assert np.allclose(Y, ref, rtol=1e-12 if dtype == np.float64 else 2e-4, atol=1e-11 if dtype == np.float64 else 2e-3)
 
 
+@pytest.mark.parametrize("rpt", [8, 7, 6])
+@pytest.mark.parametrize("n,k,dtype", [(1232, 32, np.float64), (400, 8, np.float64), (2000, 64, np.float32), (16, 16, np.float64)])
+def test_dense_matmat_tile_heights(eng, monkeypatch, rpt, n, k, dtype):
+	"""Every compiled CTA height (128, 112, 96 rows) of the warp-specialised dense kernel, with a short last row tile and
+	more chunks than pipeline stages, against NumPy (SLQ_DENSE_RPT is read at every launch)."""
+	monkeypatch.setenv("SLQ_DENSE_RPT", str(rpt))
+	rng = np.random.default_rng(n + k + rpt)
+	D = rng.standard_normal((n, n))
+	D = ((D + D.T) / 2).astype(dtype)
+	X = rng.standard_normal((n, k)).astype(dtype)
+	Y = eng.DeviceOperator(D, dtype=dtype).matmat(eng.block_from_columns(X, dtype)).cpu().numpy()
+	ref = D.astype(np.float64) @ X.astype(np.float64)
+	assert np.allclose(Y, ref, rtol=1e-12 if dtype == np.float64 else 2e-4, atol=1e-10 if dtype == np.float64 else 5e-3)
+
+
 def test_lanczos_dense_tiled_vs_oracle(eng, oracle):
 	"""alpha/beta on a dense SPD matrix of order 256 (tiled dense kernel, k = 8) against the compiled reference."""
 	rng = np.random.default_rng(8)
