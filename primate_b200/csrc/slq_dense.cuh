@@ -19,13 +19,15 @@ template <typename T, int K, int RPT = 8>
 struct DenseTiling {
   static constexpr int TR = 16 * RPT;  // rows of Y per CTA (RPT rows per thread: 128, 112 or 96)
   static constexpr int KC = 16;       // columns of A (rows of X) per stage
-  static constexpr int STAGES = 4;
-  static constexpr int NCONS = 128;   // consumer threads: 8 (column groups) x 16 (row groups)
-  static constexpr int NTD = NCONS + 32;  // + one producer warp
-  static constexpr int CW = K / 8;    // columns per thread
   static constexpr size_t A_BYTES = (size_t)KC * TR * sizeof(T);
   static constexpr size_t X_BYTES = (size_t)KC * K * sizeof(T);
   static constexpr size_t STAGE_BYTES = A_BYTES + X_BYTES;
+  // as many stages as fit beside a second resident CTA (2 x 110 KB of the SM's 227 KB), between 3 and 8
+  static constexpr int STAGES_FIT = (int)((110 * 1024) / STAGE_BYTES);
+  static constexpr int STAGES = STAGES_FIT > 8 ? 8 : (STAGES_FIT < 3 ? 3 : STAGES_FIT);
+  static constexpr int NCONS = 128;   // consumer threads: 8 (column groups) x 16 (row groups)
+  static constexpr int NTD = NCONS + 32;  // + one producer warp
+  static constexpr int CW = K / 8;    // columns per thread
   static constexpr size_t SMEM_BYTES = STAGE_BYTES * STAGES;
 };
 
