@@ -84,6 +84,13 @@ int slq_profile_read(int kernel_class, double* total_ms, long long* timed_launch
  * recommended (keeps the summation order of Eigen's column sweep) but not required. */
 int slq_csr_create(int64_t n, int64_t nnz, const int32_t* rowptr_dev, const int32_t* colidx_dev,
                    const void* vals_dev, int dtype, slq_op** out);
+/* As slq_csr_create, with the longest row given by the caller (it selects the SpMM variant: rows of more than 64
+ * non-zeros take the non-zero-balanced kernel).  max_row_nnz >= 0: trusted, the call does no device work and never
+ * synchronises (a host-ingested matrix knows its row lengths).  max_row_nnz < 0: computed by a kernel enqueued on
+ * `stream` -- after whatever is still producing the CSR arrays there -- and `stream` is synchronised to read it back;
+ * this is the ONLY entry point of the library that synchronises.  slq_csr_create == slq_csr_create_ex(.., -1, NULL). */
+int slq_csr_create_ex(int64_t n, int64_t nnz, const int32_t* rowptr_dev, const int32_t* colidx_dev,
+                      const void* vals_dev, int dtype, int64_t max_row_nnz, slq_stream stream, slq_op** out);
 /* Dense symmetric n x n, leading dimension ld (row- or column-major is the same for a symmetric matrix). */
 int slq_dense_create(int64_t n, const void* A_dev, int64_t ld, int dtype, slq_op** out);
 /* Matrix-free operator driven by a callback (device panels in, device panels out). */
@@ -158,6 +165,12 @@ int slq_quadrature(const void* alpha_dev, const void* beta_dev, int dtype, int k
 int slq_funm_coeffs(const void* alpha_dev, const void* beta_dev, int dtype, int k, int deg, int ld, int fun,
                     const double* params, double* coeffs_dev, double* theta_dev, double* tau_dev,
                     double* scratch_dev, int32_t* info_dev, slq_stream stream);
+/* Batched in-place implicit-shift QL with the contract of the reference's Pythran kernel `tqli(d, e, Z, max_iter)`
+ * (src/primate/tqli.py:15-90): d_dev k x m diagonals -> eigenvalues in the order the sweep leaves them (NOT sorted);
+ * e_dev k x m off-diagonals with a leading zero (e[i] couples i-1 and i) -> the negligible remainders; Zt_dev NULL, or
+ * k x m x m with Zt[p][col][row] = Z[row][col] (the reference's Z, transposed): on return Z <- Z_in * eigenvectors.
+ * At most max_iter sweeps per eigenvalue (tqli.py:54-56 tolerates running out; info_dev, if given, counts them). */
+int slq_tqli(double* d_dev, double* e_dev, double* Zt_dev, int k, int m, int max_iter, int32_t* info_dev, slq_stream stream);
 /* y[p] = scale[p] * sum_i f(theta[p][i]) * tau[p][i]   (fused evaluation on caller-provided nodes). */
 int slq_apply_fun(const double* theta_dev, const double* tau_dev, int k, int deg, int fun, const double* params,
                   const double* scale_dev, double* y_dev, slq_stream stream);

@@ -34,6 +34,7 @@ _SIGNATURES = {
 	"slq_profile_enable": (c_int, [c_int]),
 	"slq_profile_read": (c_int, [c_int, POINTER(c_double), POINTER(ctypes.c_longlong), POINTER(ctypes.c_longlong)]),
 	"slq_csr_create": (c_int, [c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_int, POINTER(c_void_p)]),
+	"slq_csr_create_ex": (c_int, [c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_int, c_int64, c_void_p, POINTER(c_void_p)]),
 	"slq_dense_create": (c_int, [c_int64, c_void_p, c_int64, c_int, POINTER(c_void_p)]),
 	"slq_callback_create": (c_int, [c_int64, c_int, MATMAT_FN, c_void_p, POINTER(c_void_p)]),
 	"slq_op_destroy": (c_int, [c_void_p]),
@@ -56,6 +57,7 @@ _SIGNATURES = {
 	                           c_void_p, c_void_p, c_void_p, c_void_p]),
 	"slq_funm_coeffs": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, POINTER(c_double), c_void_p, c_void_p,
 	                            c_void_p, c_void_p, c_void_p, c_void_p]),
+	"slq_tqli": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
 	"slq_apply_fun": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, POINTER(c_double), c_void_p, c_void_p, c_void_p]),
 	"slq_fttr": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
 	"slq_stats_update": (c_int, [c_void_p, c_int, c_void_p, c_void_p]),
@@ -74,10 +76,10 @@ def lib() -> ctypes.CDLL:
 	global _LIB
 	if _LIB is None:
 		path = lib_path()
-		if not os.path.exists(path):
+		if "SLQ_LIB" not in os.environ:
 			from . import _build
 
-			_build.build(verbose=False)
+			_build.build(verbose=False)  # content-hash check: a stale or missing library is rebuilt, never loaded silently
 		L = ctypes.CDLL(path)
 		for name, (res, args) in _SIGNATURES.items():
 			fn = getattr(L, name)

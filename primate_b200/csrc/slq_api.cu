@@ -22,17 +22,30 @@ int fail(int code, const char* fmt, ...) {
   return code;
 }
 
-int sm_count() {
-  static int cached = -2;
-  if (cached == -2) {
-    int dev = 0, sms = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) {
-      cudaGetLastError();
-      return -1;  // do not cache: a device may be selected later
-    }
-    cached = sms;
+int current_device() {
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess) {
+    cudaGetLastError();
+    return -1;
   }
-  return cached;
+  return dev;
+}
+
+int sm_count() {
+  static std::atomic<int> cached[MAX_DEVICES];  // zero-initialised: 0 = not queried yet
+  const int dev = current_device();
+  if (dev < 0) return -1;  // nothing cached: a device may be selected later
+  if (dev < MAX_DEVICES) {
+    const int c = cached[dev].load(std::memory_order_relaxed);
+    if (c > 0) return c;
+  }
+  int sms = 0;
+  if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) {
+    cudaGetLastError();
+    return -1;
+  }
+  if (dev < MAX_DEVICES) cached[dev].store(sms, std::memory_order_relaxed);
+  return sms;
 }
 
 static std::atomic<long long> g_launches{0};

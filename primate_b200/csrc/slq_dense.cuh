@@ -142,10 +142,10 @@ static bool dense_tma_ok(const slq_op* op, const T* X, const T* Y) {
 template <typename T, int K, int RPT>
 static int launch_dense_tma_rpt(const slq_op* op, const T* X, T* Y, cudaStream_t st) {
   using D = DenseTiling<T, K, RPT>;
-  static bool configured = false;
-  if (!configured) {
+  static DeviceOnce once;
+  if (once.needed()) {
     SLQ_CUDA(cudaFuncSetAttribute(k_dense_tma<T, K, RPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)D::SMEM_BYTES));
-    configured = true;
+    once.done();
   }
   k_dense_tma<T, K, RPT><<<(unsigned)((op->n + D::TR - 1) / D::TR), D::NTD, D::SMEM_BYTES, st>>>((int)op->n, (const T*)op->dense,
                                                                                                     op->ld, X, Y);

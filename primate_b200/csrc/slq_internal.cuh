@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <atomic>
 #include <cstdarg>
 #include <cstdio>
 
@@ -38,7 +39,26 @@ int fail(int code, const char* fmt, ...);
     if (!(cond)) return ::slq::fail(SLQ_ERR_ARG, __VA_ARGS__); \
   } while (0)
 
-int sm_count();  // cached; <= 0 if no device
+int sm_count();  // SM count of the CURRENT device (cached per device ordinal); <= 0 if no device
+
+// Per-device "done once" bookkeeping for cudaFuncSetAttribute and friends: a process may drive several GPUs (one
+// handle per device, SURVEY 8b "thread-compatible per handle"), so nothing is cached per process.  Usage:
+//   static DeviceOnce once;  if (once.needed()) { ...configure...; once.done(); }
+// Two threads may both configure (idempotent calls); the bit is only set AFTER the configuration succeeded, so no
+// thread can launch on a device whose attributes are still unset.
+constexpr int MAX_DEVICES = 64;
+int current_device();  // cudaGetDevice, or -1
+struct DeviceOnce {
+  std::atomic<unsigned long long> mask{0ull};
+  bool needed() const {
+    const int d = current_device();
+    return d < 0 || d >= MAX_DEVICES || !((mask.load(std::memory_order_acquire) >> d) & 1ull);
+  }
+  void done() {
+    const int d = current_device();
+    if (d >= 0 && d < MAX_DEVICES) mask.fetch_or(1ull << d, std::memory_order_release);
+  }
+};
 void count_launch();  // host-side counter of kernels launched by the library (slq_launch_count)
 
 // Optional per-kernel-class timing with CUDA events on the launching stream (slq_profile_*): used by bench.py to

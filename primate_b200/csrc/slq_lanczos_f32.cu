@@ -1,0 +1,7 @@
+// Explicit instantiation of the probe-blocked Lanczos driver for float panels (see slq_lanczos_impl.cuh).
+#include "slq_lanczos_impl.cuh"
+
+namespace slq {
+template int lanczos_dispatch<float>(slq_op*, void*, int, int, double, int, int, void*, void*, int32_t*, double*, void*, char*, cudaStream_t);
+template int matmat_dispatch<float>(slq_op*, const void*, void*, int, cudaStream_t);
+}  // namespace slq

@@ -67,8 +67,13 @@ constexpr int QL_MAXIT = 60;
 
 // Implicit QL on the warp's shared (d, e, z).  e[i] couples rows i and i+1 (e[m-1] unused, kept 0).
 // If Zt != nullptr the full eigenvector matrix is accumulated: Zt[col*m + row] (column-contiguous so the lanes'
-// rows are adjacent in memory).  Returns the number of eigenvalues that ran out of iterations.
-__device__ int warp_ql(double* d, double* e, double* z, int m, double* Zt) {
+// rows are adjacent in memory).  Returns the number of eigenvalues that ran out of iterations (`maxit` per
+// eigenvalue, the reference's `max_iter`, tqli.py:15,54-56).
+// Every lane executes the scalar chain redundantly on the SHARED (d, e, z).  Each rotation therefore reads everything
+// it needs, meets at a __syncwarp, writes, and meets again after the eigenvector update: under independent thread
+// scheduling a lane that owns no eigenvector row (m % 32 != 0) could otherwise run ahead and overwrite e[i], d[i],
+// z[i] before the others have read them.
+__device__ int warp_ql(double* d, double* e, double* z, int m, double* Zt, int maxit) {
   const int lane = threadIdx.x & 31;
   int nfail = 0;
   for (int l = 0; l < m; ++l) {
@@ -91,7 +96,7 @@ __device__ int warp_ql(double* d, double* e, double* z, int m, double* Zt) {
         }
       }
       if (split == l) break;  // d[l] is an eigenvalue
-      if (iter++ >= QL_MAXIT) {
+      if (iter++ >= maxit) {
         ++nfail;
         break;
       }
@@ -104,25 +109,27 @@ __device__ int warp_ql(double* d, double* e, double* z, int m, double* Zt) {
       bool deflated = false;
       __syncwarp();
       for (int i = split - 1; i >= l; --i) {
-        const double ei = e[i];
+        // ---- reads
+        const double ei = e[i], di = d[i], dip = d[i + 1], z1 = z[i + 1], z0 = z[i];
+        __syncwarp();
+        // ---- arithmetic and writes (every lane writes the same values)
         const double f = s * ei, b = c * ei;
         r = hypot(f, g);
         e[i + 1] = r;
         if (r == 0.0) {  // exact underflow of the bulge: split here and restart
-          d[i + 1] -= p;
+          d[i + 1] = dip - p;
           e[split] = 0.0;
           deflated = true;
           break;
         }
         s = f / r;
         c = g / r;
-        const double di1 = d[i + 1] - p;
-        r = (d[i] - di1) * s + 2.0 * c * b;
+        const double di1 = dip - p;
+        r = (di - di1) * s + 2.0 * c * b;
         p = s * r;
         d[i + 1] = di1 + p;
         g = c * r - b;
         // plane rotation (c, s) acting on eigenvector columns i, i+1
-        const double z1 = z[i + 1], z0 = z[i];
         z[i + 1] = s * z0 + c * z1;
         z[i] = c * z0 - s * z1;
         if (Zt) {
@@ -132,15 +139,46 @@ __device__ int warp_ql(double* d, double* e, double* z, int m, double* Zt) {
             Zt[(size_t)i * m + row] = c * y0 - s * y1;
           }
         }
+        __syncwarp();
       }
+      __syncwarp();
       if (deflated) continue;
-      d[l] -= p;
+      const double dl2 = d[l];
+      __syncwarp();
+      d[l] = dl2 - p;
       e[l] = g;
       e[split] = 0.0;
     }
   }
   __syncwarp();
   return nfail;
+}
+
+// In-place batched implicit QL with the contract of the reference's `tqli(d, e, Z, max_iter)` (tqli.py:15-90): on
+// return d holds the eigenvalues in the order the QL sweep left them (NOT sorted), e the (negligible) off-diagonals,
+// and, when Zt is given, Zt <- (incoming Z) x (eigenvectors of T), stored column-contiguous.  e has a leading zero on
+// input (e[i] couples i-1 and i) as in the reference.
+__global__ void k_tqli(double* __restrict__ d_io, double* __restrict__ e_io, double* __restrict__ Zt_io, int k, int m, int maxit,
+                       int32_t* __restrict__ info) {
+  extern __shared__ double sm[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int p = blockIdx.x * (blockDim.x >> 5) + warp;
+  if (p >= k) return;
+  double* d = sm + (size_t)warp * 3 * m;
+  double* e = d + m;
+  double* z = e + m;
+  for (int i = lane; i < m; i += 32) {
+    d[i] = d_io[(size_t)p * m + i];
+    e[i] = (i + 1 < m) ? e_io[(size_t)p * m + i + 1] : 0.0;  // shift: e[i] couples i and i+1
+    z[i] = (i == 0) ? 1.0 : 0.0;
+  }
+  __syncwarp();
+  const int nfail = warp_ql(d, e, z, m, Zt_io ? Zt_io + (size_t)p * m * m : nullptr, maxit);
+  if (info && lane == 0) info[p] = nfail;
+  for (int i = lane; i < m; i += 32) {
+    d_io[(size_t)p * m + i] = d[i];
+    e_io[(size_t)p * m + i] = (i == 0) ? 0.0 : e[i - 1];
+  }
 }
 
 // One warp per matrix.  Dynamic shared memory: 5*deg doubles per warp (d, e, z, sorted theta, sorted tau/g).
@@ -170,7 +208,7 @@ __global__ void k_quadrature(const T* __restrict__ alpha, const T* __restrict__ 
     for (int idx = lane; idx < deg * deg; idx += 32) Zt[idx] = (idx / deg == idx % deg) ? 1.0 : 0.0;
   }
   __syncwarp();
-  const int nfail = warp_ql(d, e, z, deg, Zt);
+  const int nfail = warp_ql(d, e, z, deg, Zt, QL_MAXIT);
   if (info && lane == 0) info[p] = nfail;
 
   // rank-sort ascending (LAPACK order, so nodes/weights line up with the reference's)
@@ -345,6 +383,21 @@ int slq_funm_coeffs(const void* alpha_dev, const void* beta_dev, int dtype, int 
                                                       info_dev, scratch_dev, coeffs_dev, st)
                           : quadrature_launch<float>(alpha_dev, beta_dev, k, deg, ld, fun, prm, nullptr, theta_dev, tau_dev, nullptr,
                                                      info_dev, scratch_dev, coeffs_dev, st);
+}
+
+int slq_tqli(double* d_dev, double* e_dev, double* Zt_dev, int k, int m, int max_iter, int32_t* info_dev, slq_stream stream) {
+  SLQ_REQUIRE(d_dev && e_dev, "NULL argument");
+  SLQ_REQUIRE(k > 0 && m > 0 && max_iter >= 0, "invalid shape k=%d m=%d max_iter=%d", k, m, max_iter);
+  if (sm_count() <= 0) return fail(SLQ_ERR_CUDA, "no CUDA device");
+  const size_t per_warp = sizeof(double) * 3 * (size_t)m;
+  int w = 4;
+  while (w > 1 && per_warp * w > 200 * 1024) w >>= 1;
+  if (per_warp * w > 220 * 1024) return fail(SLQ_ERR_UNSUPPORTED, "m=%d too large for the shared-memory eigensolver", m);
+  const size_t smem = per_warp * w;
+  if (smem > 48 * 1024) SLQ_CUDA(cudaFuncSetAttribute(k_tqli, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  k_tqli<<<(unsigned)((k + w - 1) / w), w * 32, smem, (cudaStream_t)stream>>>(d_dev, e_dev, Zt_dev, k, m, max_iter, info_dev);
+  SLQ_LAUNCH_CHECK();
+  return SLQ_OK;
 }
 
 int slq_apply_fun(const double* theta_dev, const double* tau_dev, int k, int deg, int fun, const double* params, const double* scale_dev,

@@ -576,11 +576,11 @@ static int launch_stepA_tma(const slq_op* op, const T* uc, const T* up, T* w, Lz
                             double* partial, const StepOut& so, cudaStream_t st) {
   using C = TmaTiling<T, K>;
   using CB = TmaTiling<T, K, true>;
-  static bool configured = false;
-  if (!configured) {
+  static DeviceOnce once;  // per (T, K, MODE) instantiation, tracked per device
+  if (once.needed()) {
     SLQ_CUDA(cudaFuncSetAttribute(k_stepA_tma<T, K, MODE, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM_BYTES));
     SLQ_CUDA(cudaFuncSetAttribute(k_stepA_tma<T, K, MODE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CB::SMEM_BAL));
-    configured = true;
+    once.done();
   }
   const int n = (int)op->n;
   const int ntiles = (n + C::TILE - 1) / C::TILE;

@@ -199,8 +199,9 @@ class DeviceOperator:
 			if self.perm is not None and not balance:
 				self.h2d_bytes += self.perm.numel() * 4
 			self.kind, self.nnz = "csr", int(C.nnz)
-			_ffi.check(L.slq_csr_create(self.n, self.nnz, rowptr.data_ptr(), colidx.data_ptr(), vals.data_ptr(), self.code,
-			                            ctypes.byref(self._handle)))  # fmt: skip
+			# the longest row is known on the host (a symmetric permutation keeps the row lengths): no device work, no sync
+			_ffi.check(L.slq_csr_create_ex(self.n, self.nnz, rowptr.data_ptr(), colidx.data_ptr(), vals.data_ptr(), self.code,
+			                               int(np.diff(C.indptr).max(initial=0)), None, ctypes.byref(self._handle)))  # fmt: skip
 		elif isinstance(A, np.ndarray) or (hasattr(A, "is_cuda") and hasattr(A, "data_ptr")):
 			M = A if hasattr(A, "data_ptr") else torch.from_numpy(np.ascontiguousarray(A, dtype=self.dtype))
 			M = M.to(dev, dtype=_tdtype(self.dtype)).contiguous()
@@ -256,8 +257,9 @@ class DeviceOperator:
 		self._keep = [rowptr, colidx, vals]
 		self.kind, self.nnz = "csr", int(colidx.numel())
 		self._handle = ctypes.c_void_p()
-		_ffi.check(L.slq_csr_create(self.n, self.nnz, rowptr.data_ptr(), colidx.data_ptr(), vals.data_ptr(), self.code,
-		                            ctypes.byref(self._handle)))  # fmt: skip
+		# longest row computed on the CURRENT stream (the arrays may still be in flight there) and read back: documented sync
+		_ffi.check(L.slq_csr_create_ex(self.n, self.nnz, rowptr.data_ptr(), colidx.data_ptr(), vals.data_ptr(), self.code,
+		                               -1, _stream_ptr(), ctypes.byref(self._handle)))  # fmt: skip
 		self._ws = {}
 		return self
 

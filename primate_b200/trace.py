@@ -59,15 +59,28 @@ def _sample_range(sample_block: Callable, lo: int, hi: int, kmax: int):
 
 
 def _pad(y, m: int):
-	"""Pads a (<= m,) sample vector to length m with NaN so that every rank contributes the same size."""
+	"""Pads a (<= m,) sample vector to length m (zeros) so that every rank contributes the same size."""
 	have = int(y.shape[0])
 	if have == m:
 		return y
 	if hasattr(y, "detach"):
 		import torch
 
-		return torch.cat([y, torch.full((m - have,), float("nan"), dtype=y.dtype, device=y.device)])
-	return np.concatenate([np.asarray(y, dtype=np.float64), np.full(m - have, np.nan)])
+		return torch.cat([y, torch.zeros((m - have,), dtype=y.dtype, device=y.device)])
+	return np.concatenate([np.asarray(y, dtype=np.float64), np.zeros(m - have)])
+
+
+def _gather_ranges(y, total: int, comm) -> np.ndarray:
+	"""All ranks' samples of a `total`-probe range in global probe order.  Every rank's row of the gathered table is
+	cut to the length `probe_range` assigns it -- a genuine NaN sample (QL non-convergence, inv/sqrt of a bad Ritz
+	value) is kept and reaches the estimator exactly as it would on one rank."""
+	per = -(-int(total) // comm.size)
+	table = comm.all_gather(_pad(y, per)).reshape(comm.size, per)
+	parts = []
+	for r in range(comm.size):
+		lo, hi = sharding.probe_range(total, r, comm.size)
+		parts.append(table[r, : hi - lo])
+	return np.concatenate(parts)
 
 
 def _run_fixed_count(sample_block, estimator, total: int, comm, kmax: int, stats_fn=None) -> int:
@@ -82,9 +95,7 @@ def _run_fixed_count(sample_block, estimator, total: int, comm, kmax: int, stats
 		for cnt, mean, m2 in comm.all_gather(rec):
 			estimator.merge(int(cnt), mean, m2)
 		return total
-	per = -(-total // comm.size)
-	allv = comm.all_gather(_pad(y, per)).ravel() if comm.size > 1 else _to_host(y)
-	allv = allv[~np.isnan(allv)] if comm.size > 1 else allv
+	allv = _gather_ranges(y, total, comm) if comm.size > 1 else _to_host(y)
 	assert allv.size == total
 	if total > 1:
 		estimator.update(allv[:-1])
@@ -112,12 +123,7 @@ def _run_batched(sample_block, estimator, converge, batch: int, callback, result
 	while not converge(estimator):
 		lo, hi = sharding.probe_range(batch, comm.rank, comm.size)
 		y = _sample_range(sample_block, consumed + lo, consumed + hi, kmax)
-		if comm.size > 1:
-			per = -(-batch // comm.size)
-			vals = comm.all_gather(_pad(y, per)).ravel()
-			vals = vals[~np.isnan(vals)]
-		else:
-			vals = _to_host(y)
+		vals = _gather_ranges(y, batch, comm) if comm.size > 1 else _to_host(y)
 		estimator.update(vals)
 		consumed += batch
 		callback(result)

@@ -55,13 +55,20 @@ def eigvalsh_tridiag(d: np.ndarray, e: np.ndarray, method: str = "auto", maxiter
 
 
 def tqli(d: np.ndarray, e: np.ndarray, Z: np.ndarray, max_iter: int = 30) -> None:
-	"""In-place contract of the reference's Pythran kernel (tqli.py:15): on return `d` holds the eigenvalues and, when
-	Z is m x m, its columns the eigenvectors of the input matrix times the incoming Z.  `e` has a leading zero."""
-	dd, ee, _ = _prep(np.array(d, copy=True), np.array(e, copy=True))
-	if np.prod(Z.shape) == 0:
-		d[:] = _device_eigh(dd, ee, False)
-	else:
-		w, Y = _device_eigh(dd, ee, True)
-		d[:] = w
-		Z[:] = Z @ Y
-	e[:] = 0
+	"""In-place contract of the reference's Pythran kernel (tqli.py:15-90), on the device (libslq: slq_tqli): on return
+	`d` holds the eigenvalues in the order the QL sweep left them (not sorted), `e` (leading zero on input) the
+	negligible off-diagonal remainders and, when Z is m x m, Z <- Z @ (eigenvectors of T).  At most `max_iter` implicit
+	QL sweeps are spent per eigenvalue; like the reference, running out is tolerated silently."""
+	torch = engine._torch()
+	m = len(d)
+	assert len(e) == m, "`e` must have the length of `d` (leading zero)"
+	dd = torch.from_numpy(np.ascontiguousarray(d, dtype=np.float64)[None, :].copy()).cuda()
+	ee = torch.from_numpy(np.ascontiguousarray(e, dtype=np.float64)[None, :].copy()).cuda()
+	want_vectors = np.prod(Z.shape) != 0
+	Zt = torch.from_numpy(np.ascontiguousarray(np.asarray(Z, dtype=np.float64).T)[None].copy()).cuda() if want_vectors else None
+	_ffi.check(_ffi.lib().slq_tqli(dd.data_ptr(), ee.data_ptr(), Zt.data_ptr() if want_vectors else None, 1, m, int(max_iter), None,
+	                               engine._stream_ptr()))  # fmt: skip
+	d[:] = dd.cpu().numpy()[0]
+	e[:] = ee.cpu().numpy()[0]
+	if want_vectors:
+		Z[:] = Zt.cpu().numpy()[0].T
