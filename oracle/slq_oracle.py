@@ -217,9 +217,14 @@ def _ncv_for(deg: int, orth: int, return_basis: bool = False) -> tuple:
     return orth, ncv
 
 
-def ref_lanczos(A, v: np.ndarray, deg: int, rtol: float = 1e-8, orth: int = 0, ncv: Optional[int] = None):
+def ref_lanczos(A, v: np.ndarray, deg: int, rtol: float = 1e-8, orth: int = 0, ncv: Optional[int] = None,
+                Q: Optional[np.ndarray] = None):
     """One call of the reference FFI (src/primate/_lanczos.cpp:86-100) on FRESH zero buffers
-    (lanczos.py:101-103).  Returns (alpha[deg+1], beta[deg+1], Q[n, ncv])."""
+    (lanczos.py:101-103).  Returns (alpha[deg+1], beta[deg+1], Q[n, ncv]).
+
+    ``Q`` may be a caller-owned (n, ncv) F-ordered buffer that is re-used as is, the way the reference's
+    ``MatrixFunction`` re-uses ``_Q`` across probes (operators.py:138-148).  Only valid for ``orth == 0``, where the
+    result does not depend on what the stale columns hold; for ``orth > 0`` it is zeroed first."""
     ext = reference_ext()
     n = A.shape[0]
     dt = np.dtype(v.dtype)
@@ -227,7 +232,12 @@ def ref_lanczos(A, v: np.ndarray, deg: int, rtol: float = 1e-8, orth: int = 0, n
         orth, ncv = _ncv_for(deg, orth)
     alpha = np.zeros(deg + 1, dtype=dt)
     beta = np.zeros(deg + 1, dtype=dt)
-    Q = np.zeros((n, ncv), dtype=dt, order="F")
+    if Q is None:
+        Q = np.zeros((n, ncv), dtype=dt, order="F")
+    else:
+        assert Q.shape == (n, ncv) and Q.dtype == dt and Q.flags["F_CONTIGUOUS"]
+        if orth > 0:
+            Q.fill(0)
     ext.lanczos(A, np.array(v, dtype=dt, copy=True), deg, rtol, orth, alpha, beta, Q)
     return alpha, beta, Q
 
@@ -358,16 +368,42 @@ def ref_quad(A, X: np.ndarray, fun="identity", deg: int = 20, orth: int = 0, rto
     X = X[:, None] if X.ndim == 1 else X
     y = np.zeros(X.shape[1])
     extra = []
+    # one basis buffer for all columns, as the reference holds `_Q` (operators.py:74,138-148) -- without it every probe
+    # would page-fault a fresh n x deg array (400 MB at config C2), a cost the reference does not pay
+    kw = {"Q": np.zeros((n, deg), dtype=np.dtype(dtype), order="F")} if lanczos is ref_lanczos else {}
     for j in range(X.shape[1]):
         xc = X[:, j]
         x_norm_sq = np.linalg.norm(xc) ** 2  # operators.py:147
-        out = lanczos(A, xc, deg, rtol, orth, ncv=deg)
+        out = lanczos(A, xc, deg, rtol, orth, ncv=deg, **kw)
         alpha, beta = out[0], out[1]
         theta, tau = ref_quadrature(alpha, beta, deg)  # operators.py:149
         y[j] = np.sum(f(theta) * tau, axis=-1) * x_norm_sq  # operators.py:150
         if return_all:
             extra.append((alpha.copy(), beta.copy(), theta, tau))
     return (y, extra) if return_all else y
+
+
+def ref_matvec(A, x: np.ndarray, fun="identity", deg: int = 20, orth: int = 0, rtol: float = 1e-8, dtype=np.float64, **fun_kw):
+    """operators.py:102-124: y = ||x|| Q Y (f(theta) o Y[0,:])^T with the full basis (ncv = deg), zeroed per call
+    (operators.py:116), SciPy eigh_tridiagonal for (theta, Y) (tridiag.py:10-11).  x: (n,) or (n, m) -> same shape."""
+    from scipy.linalg import eigh_tridiagonal
+
+    f = spectral_fun(fun, **fun_kw)
+    n = A.shape[0]
+    deg = min(deg, n)
+    orth = deg if orth < 0 or orth > deg else orth
+    X = np.asarray(x, dtype=dtype)
+    cols = X[:, None] if X.ndim == 1 else X
+    out = np.empty(cols.shape, dtype=np.dtype(dtype), order="F")
+    Q = np.zeros((n, deg), dtype=np.dtype(dtype), order="F")
+    for j in range(cols.shape[1]):
+        xc = np.ascontiguousarray(cols[:, j])
+        x_norm = np.linalg.norm(xc)
+        Q.fill(0)  # operators.py:116
+        alpha, beta, _ = ref_lanczos(A, xc, deg, rtol, orth, ncv=deg, Q=Q)
+        rw, Y = eigh_tridiagonal(alpha[:deg], beta[1:deg])  # operators.py:122
+        out[:, j] = x_norm * (Q @ (Y @ (np.ravel(f(rw)) * Y[0, :])))  # operators.py:124
+    return out[:, 0] if X.ndim == 1 else out
 
 
 class Welford:
@@ -413,3 +449,98 @@ def ref_hutch(A, fun="identity", deg: int = 20, orth: int = 0, count: int = 200,
         est.update(y)
         samples.extend(y.tolist())
     return (est.mu, np.array(samples)) if return_samples else est.mu
+
+
+# --------------------------------------------------------------------------------------------------
+# block drivers: src/primate/trace.py:119-315, diagonal.py:11-138 (host algebra on a `matmat` callable)
+# --------------------------------------------------------------------------------------------------
+def _coldots(X, Y):
+    """diag(X^T Y) as a column (the reference's `diag_prod`, trace.py:201 / diagonal.py:111)."""
+    return np.einsum("ij,ij->j", X, Y)[:, None]
+
+
+def ref_hutchpp(matmat: Callable, n: int, m: int, pdf: str = "rademacher", seed=None, dtype=np.float64, quad: Optional[Callable] = None):
+    """trace.py:135-182: sketch Q = qr(A W), exact trace on range(Q) (`quad` per column in "reduced" mode, else
+    diag(Q^T A Q)), Hutchinson on the deflated remainder.  Returns (estimate, samples)."""
+    rng = np.random.default_rng(seed)
+    nb = m + m % 3  # trace.py:153-154
+    WB = ref_isotropic((n, nb), pdf, rng).astype(dtype)  # trace.py:159
+    Q = np.linalg.qr(matmat(WB), mode="reduced")[0]  # trace.py:160
+    rng_ests = np.ravel(quad(Q)) if quad is not None else np.einsum("ij,ij->j", matmat(Q), Q)  # trace.py:168
+    G = ref_isotropic((n, nb), pdf, rng).astype(dtype)  # trace.py:172
+    G -= Q @ (Q.T @ G)  # trace.py:173
+    defl_ests = np.einsum("ij,ij->j", matmat(G), G)  # trace.py:174
+    est = np.sum(rng_ests) + np.sum(defl_ests) / nb  # trace.py:169,175-178
+    return est, np.concatenate([np.ravel(rng_ests), defl_ests])
+
+
+def ref_xdiag(matmat: Callable, n: int, m: Optional[int] = None, pdf: str = "sphere", seed=None):
+    """diagonal.py:99-138 (XDiag) on a symmetric operator (A.T @ Q == A @ Q)."""
+    m = 2 * n if m is None else min(m + (m % 2), 2 * n)  # diagonal.py:107
+    m = m // 2
+    rng = np.random.default_rng(seed=seed)
+    N = ref_isotropic((n, m), pdf, rng)  # diagonal.py:115
+    Y = matmat(N)
+    Q, R = np.linalg.qr(Y, mode="reduced")  # diagonal.py:117
+    rowdot = lambda X, Z: np.einsum("ij,ij->i", X, Z)[:, None]  # noqa: E731  (diag_prod(X.T, Z.T), diagonal.py:111)
+    dNY = rowdot(N, Y)
+    Z = matmat(Q)  # diagonal.py:123
+    T = Z.T @ N
+    R_inv = np.linalg.inv(R)
+    S = R_inv.T / np.linalg.norm(R_inv, axis=1)  # diagonal.py:126
+    QS = Q @ S
+    dQZ, dQSSZ, dNTQ = rowdot(Q, Z), rowdot(QS, Z @ S), rowdot(N, Q @ T)  # diagonal.py:130-132
+    dNQSST = rowdot(N, QS * _coldots(S, T).T)  # diagonal.py:133
+    return (dQZ + (-dQSSZ + dNY - dNTQ + dNQSST) / m).ravel()  # diagonal.py:137
+
+
+def _ref_xtrace_samples(W, Z, Q, R, R_inv):
+    """trace.py:185-227 with the non-"sphere" scale (xtrace hands `_xtrace` the sampler callable, so the sphere branch
+    at trace.py:209-214 is never taken: SURVEY A.2)."""
+    m = W.shape[1]
+    Wp = Q.T @ W
+    S = R_inv.T / np.linalg.norm(R_inv, axis=1)  # trace.py:206
+    H = Q.T @ Z
+    HW = H @ Wp
+    T = Z.T @ W
+    dSW, dSHS = _coldots(S, Wp), _coldots(S, H @ S)
+    dTW, dWHW = _coldots(T, Wp), _coldots(Wp, HW)
+    dSRmHW, dTmHRS = _coldots(S, R - HW), _coldots(T - H.T @ Wp, S)
+    ests = np.trace(H) * np.ones((m, 1)) - dSHS  # trace.py:224
+    ests += -dTW + dWHW + dSW * dSRmHW + np.abs(dSW) ** 2 * dSHS + dTmHRS * dSW  # trace.py:225
+    return ests
+
+
+def ref_xtrace(matmat: Callable, n: int, batch: int = 32, pdf: str = "sphere", seed=None, max_samples: Optional[int] = None):
+    """trace.py:268-315: grows W, Q, R, Z batch by batch until n samples (the reference's CountCriterion(n) is always
+    in force, trace.py:271-276); `max_samples` truncates the loop for tests.  Returns (estimate, per-batch estimates)."""
+    rng = np.random.default_rng(seed)
+    stop = n if max_samples is None else min(n, max_samples)
+    W, Ymat, Z = np.zeros((n, 0)), np.zeros((n, 0)), np.zeros((n, 0))
+    history, est = [], np.nan
+    while W.shape[1] < stop:
+        ns = min(n - W.shape[1], int(batch))  # trace.py:289
+        Nw = ref_isotropic((n, ns), pdf, rng)
+        Ymat = np.c_[Ymat, matmat(Nw)]
+        Q, R = np.linalg.qr(Ymat, mode="reduced")  # == the qr_insert sequence up to column signs, which cancel in _xtrace
+        R_inv = np.linalg.inv(R)
+        W = np.c_[W, Nw]
+        Z = np.c_[Z, matmat(Q[:, -ns:])]  # trace.py:303 -- NB images of the columns as they were when appended
+        # qr_insert keeps earlier columns of Q fixed, so Z's earlier columns stay valid (QR of a prefix is a prefix)
+        est = float(np.mean(_ref_xtrace_samples(W, Z, Q, R, R_inv)))
+        history.append(est)
+    return est, history
+
+
+def ref_diag(matmat: Callable, n: int, count: int, pdf: str = "rademacher", seed=None, dtype=np.float64):
+    """diagonal.py:84-91 with converge="count": running ratio sum(v * Av) / sum(v * v), averaged per probe by a
+    MeanEstimator(dim=n) (estimators.py:128-141)."""
+    rng = np.random.default_rng(seed)
+    numer, denom, mu = np.zeros(n, dtype=dtype), np.zeros(n, dtype=dtype), np.zeros(n)
+    for i in range(count):
+        v = ref_isotropic((n, 1), pdf, rng).astype(dtype)
+        u = np.ravel(matmat(v))
+        numer += u * v.ravel()
+        denom += np.square(v.ravel())
+        mu += ((numer / denom) - mu) / (i + 1)
+    return mu

@@ -143,3 +143,24 @@ def test_doc_known_answers(golden):
     assert golden["A150_trace"].item() == 74.88426089840914
     assert abs(golden["A150_logdet"].item() - (-151.5297634573417)) < 1e-12
     assert abs(golden["quad_log_v42"].item() - (-138.90995746812578)) < 1e-12
+
+
+def test_block_driver_restatements_match_reference_goldens(oracle, golden):
+	"""oracle.ref_hutchpp / ref_xdiag / ref_xtrace / ref_diag (restated host algebra of trace.py:119-315 and
+	diagonal.py:11-138) against values produced by the unmodified reference on the same matrix and seeds."""
+	A = golden["A150"]
+	mm = lambda X: A @ X  # noqa: E731
+	assert abs(oracle.ref_hutchpp(mm, 150, 30, seed=4)[0] - golden["hutchpp_A_m30_seed4"].item()) < 1e-10
+	assert np.allclose(oracle.ref_xdiag(mm, 150, 20, seed=6), golden["xdiag_A_m20_seed6"], rtol=1e-12, atol=1e-13)
+	assert abs(oracle.ref_xtrace(mm, 150, 10, seed=8)[0] - golden["xtrace_A_b10_seed8"].item()) < 1e-9
+	assert np.allclose(oracle.ref_diag(mm, 150, 50, seed=10), golden["diag_A_seed10"], rtol=1e-12, atol=1e-13)
+
+
+def test_ref_matvec_matches_reference_golden(oracle, golden):
+	"""oracle.ref_matvec (operators.py:102-124 restated around the compiled extension) against the reference's _matvec."""
+	A, v = golden["A150"], golden["v42"]
+	for fun, kw in (("log", {}), ("exp", {"t": -0.5}), ("identity", {})):
+		for orth in (0, 20):
+			y = oracle.ref_matvec(A, v, fun, deg=20, orth=orth, **kw)
+			g = golden[f"matvec_{fun}_orth{orth}_v42"]
+			assert np.max(np.abs(y - np.ravel(g))) < 1e-12 * np.max(np.abs(g))
