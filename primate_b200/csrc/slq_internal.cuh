@@ -182,6 +182,19 @@ __device__ __forceinline__ void st_pack(T* p, const Pack<T, V>& x) {
   }
 }
 
+// Explicitly rounded products and fused multiply-subtracts for the recurrence arithmetic.  The three-term recurrence is
+// evaluated by several kernels (the fused SpMM epilogues, the streaming axpy, the basis-free replay of f(A) X): spelling
+// the contraction out -- instead of leaving `a * b - c * d` to the compiler's per-kernel choice -- makes every one of
+// them produce bit-identical Lanczos vectors, which the two-pass f(A) X engine relies on.
+__device__ __forceinline__ double mul_rn(double a, double b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ float mul_rn(float a, float b) { return __fmul_rn(a, b); }
+// c - a * b, one rounding
+__device__ __forceinline__ double fnma_rn(double a, double b, double c) { return __fma_rn(-a, b, c); }
+__device__ __forceinline__ float fnma_rn(float a, float b, float c) { return __fmaf_rn(-a, b, c); }
+// a * b + c, one rounding
+__device__ __forceinline__ double fma_rn(double a, double b, double c) { return __fma_rn(a, b, c); }
+__device__ __forceinline__ float fma_rn(float a, float b, float c) { return __fmaf_rn(a, b, c); }
+
 // Probe-block thread mapping for scalar type T and block width K: each thread owns V adjacent probes of a row (one
 // 32-byte access); LPR threads cover one row.
 template <typename T, int K>

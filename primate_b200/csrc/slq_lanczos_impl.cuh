@@ -190,11 +190,11 @@ __global__ void __launch_bounds__(NT)
         Pack<T, V> wv;
         if (FIRST) {
 #pragma unroll
-          for (int q = 0; q < V; ++q) wv.v[q] = acc[q] * rc[q];
+          for (int q = 0; q < V; ++q) wv.v[q] = mul_rn(acc[q], rc[q]);
         } else {
           Pack<T, V> pv = ld_pack<T, V, LD_STREAM>(up + r * K + slot);
 #pragma unroll
-          for (int q = 0; q < V; ++q) wv.v[q] = acc[q] * rc[q] - brp[q] * pv.v[q];
+          for (int q = 0; q < V; ++q) wv.v[q] = fnma_rn(brp[q], pv.v[q], mul_rn(acc[q], rc[q]));
         }
         st_pack<T, V, false>(w + r * K + slot, wv);
 #pragma unroll
@@ -391,7 +391,7 @@ __global__ void __launch_bounds__(NT, SLQ_STEPA_MINB)
 #pragma unroll
         for (int q = 0; q < V; ++q) {
           const T rcq = s_rc[slot + q];
-          wv.v[q] = FIRST ? acc[q] * rcq : acc[q] * rcq - s_brp[slot + q] * pv.v[q];
+          wv.v[q] = FIRST ? mul_rn(acc[q], rcq) : fnma_rn(s_brp[slot + q], pv.v[q], mul_rn(acc[q], rcq));
           acc_a[0][q] += (double)(qc.v[q] * rcq) * (double)wv.v[q];
         }
         st_pack<T, V, false>(w + off, wv);
@@ -485,7 +485,7 @@ __global__ void __launch_bounds__(NT) k_axpy(int64_t n, T* __restrict__ v, const
     Pack<T, V> a2;
     if (MODE == AX_DOT_OTHER) a2 = ld_pack<T, V, LD_DEFAULT>(u2 + e * V);
 #pragma unroll
-    for (int q = 0; q < V; ++q) vv.v[q] = vv.v[q] - cf[q] * a1.v[q];
+    for (int q = 0; q < V; ++q) vv.v[q] = fnma_rn(cf[q], a1.v[q], vv.v[q]);
     st_pack<T, V, false>(v + e * V, vv);
 #pragma unroll
     for (int q = 0; q < V; ++q) {
@@ -573,7 +573,7 @@ __global__ void __launch_bounds__(NT, 1)
       Pack<T, V> a1 = ld_pack<T, V, LD_DEFAULT>(u_prev + e * V);
       Pack<T, V> a2 = (m == 0) ? a1 : ld_pack<T, V, LD_DEFAULT>(u_cur + e * V);
 #pragma unroll
-      for (int q = 0; q < V; ++q) vv.v[q] = vv.v[q] - cf[q] * a1.v[q];
+      for (int q = 0; q < V; ++q) vv.v[q] = fnma_rn(cf[q], a1.v[q], vv.v[q]);
       s_v[l] = vv;
 #pragma unroll
       for (int q = 0; q < V; ++q) {
@@ -635,7 +635,7 @@ __global__ void __launch_bounds__(NT, 1)
     Pack<T, V> vv = s_v[l];
     Pack<T, V> a1 = ld_pack<T, V, LD_DEFAULT>(u_prev + e * V);
 #pragma unroll
-    for (int q = 0; q < V; ++q) vv.v[q] = vv.v[q] - cf[q] * a1.v[q];
+    for (int q = 0; q < V; ++q) vv.v[q] = fnma_rn(cf[q], a1.v[q], vv.v[q]);
     st_pack<T, V, false>(v + e * V, vv);
 #pragma unroll
     for (int q = 0; q < V; ++q) accn[0][q] += (double)vv.v[q] * (double)vv.v[q];
