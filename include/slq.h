@@ -188,6 +188,24 @@ int slq_stats_update(const double* y_dev, int m, double* state_dev, slq_stream s
 int slq_basis_combine(const void* Q_dev, int64_t n, int k, int deg, int dtype, const double* coeffs_dev,
                       const double* xnorm2_dev, void* Y_dev, slq_stream stream);
 
+/* ---- basis-free f(A) X: two-pass Lanczos (src/primate/operators.py:102-124 without the n x deg basis `_Q`) ------------ */
+/* Y[n x k] = f(A) X for a built-in spectral function, orth = 0.  Pass 1 runs the Lanczos recurrence on a copy of X and
+ * keeps only alpha/beta; the Krylov coefficients c_p = Y f(Theta) Y^T e_1 follow on the device; pass 2 re-runs the
+ * recurrence from the intact X with the RECORDED alpha/beta -- no grid-wide reductions, so the whole step (SpMM, both
+ * subtractions, Y += c_{j+1} ||x|| q_{j+1}) is ONE kernel for CSR operators -- producing bit-identical Lanczos vectors.
+ * Memory is five panels whatever deg is (the reference holds n x deg: 10.7 GB per probe at n = 16.7 M, deg = 80).
+ * X_dev is left intact; X_dev != Y_dev.  Workspace: slq_funm_workspace_bytes, 256-byte aligned. */
+size_t slq_funm_workspace_bytes(int64_t n, int k, int deg, int dtype);
+int slq_funm_matmat(slq_op* op, const void* X_dev, int k, int deg, double rtol, int fun, const double* params, void* Y_dev,
+                    void* workspace_dev, size_t workspace_bytes, slq_stream stream);
+/* Pass 2 on its own, for coefficients computed elsewhere (a Python callable evaluated on the host on the Ritz values):
+ * alpha/beta (k x (deg+1), the run's dtype), steps (k) and xnorm2 (k) as slq_lanczos(orth = 0, ncv = 2) left them for the
+ * SAME start block X_dev; coeffs k x deg doubles.  Y = sum_m coeffs[p][m] ||x_p|| q_m. */
+size_t slq_replay_workspace_bytes(int64_t n, int k, int deg, int dtype);
+int slq_lanczos_replay(slq_op* op, const void* X_dev, int k, int deg, const void* alpha_dev, const void* beta_dev,
+                       const int32_t* steps_dev, const double* xnorm2_dev, const double* coeffs_dev, void* Y_dev,
+                       void* workspace_dev, size_t workspace_bytes, slq_stream stream);
+
 #if defined(__GNUC__)
 #pragma GCC visibility pop
 #endif

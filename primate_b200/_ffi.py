@@ -61,6 +61,11 @@ _SIGNATURES = {
 	"slq_apply_fun": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, POINTER(c_double), c_void_p, c_void_p, c_void_p]),
 	"slq_fttr": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
 	"slq_stats_update": (c_int, [c_void_p, c_int, c_void_p, c_void_p]),
+	"slq_funm_workspace_bytes": (c_size_t, [c_int64, c_int, c_int, c_int]),
+	"slq_funm_matmat": (c_int, [c_void_p, c_void_p, c_int, c_int, c_double, c_int, POINTER(c_double), c_void_p, c_void_p, c_size_t, c_void_p]),
+	"slq_replay_workspace_bytes": (c_size_t, [c_int64, c_int, c_int, c_int]),
+	"slq_lanczos_replay": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+	                               c_size_t, c_void_p]),
 	"slq_basis_combine": (c_int, [c_void_p, c_int64, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
 }  # fmt: skip
 

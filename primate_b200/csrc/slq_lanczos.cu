@@ -176,6 +176,126 @@ int slq_lanczos(slq_op* op, void* X_dev, int k, int deg, double rtol, int orth, 
                                        (char*)workspace_dev, st);
 }
 
+// ---- basis-free f(A) X (two-pass Lanczos) -------------------------------------------------------------------------------
+namespace {
+struct ReplayWs {
+  size_t panel, table_off, y0_off, total;
+};
+ReplayWs replay_layout(int64_t n, int k, int deg, int dtype) {
+  ReplayWs w;
+  w.panel = align_up((size_t)n * k * dtype_size(dtype), 256);
+  w.table_off = 3 * w.panel;
+  w.y0_off = w.table_off + align_up(sizeof(double) * 4 * MAXK * (size_t)(deg > 0 ? deg : 1), 256);
+  w.total = w.y0_off + align_up(sizeof(double) * MAXK, 256);
+  return w;
+}
+struct FunmWs {
+  size_t panel, lz_off, table_off, y0_off, alpha_off, beta_off, steps_off, xn_off, coef_off, theta_off, tau_off, scr_off, info_off, total;
+};
+FunmWs funm_layout(int64_t n, int k, int deg, int dtype) {
+  FunmWs w;
+  const size_t s = dtype_size(dtype);
+  w.panel = align_up((size_t)n * k * s, 256);
+  size_t off = w.panel;  // [0, panel): clobberable copy of X for the first pass = replay panel 0
+  w.lz_off = off;        // Lanczos workspace (ncv = 2): its two panels double as replay panels 1 and 2
+  off += align_up(ws_layout(n, k, 2, dtype, nullptr, nullptr), 256);
+  w.table_off = off;
+  off += align_up(sizeof(double) * 4 * MAXK * (size_t)deg, 256);
+  w.y0_off = off;
+  off += align_up(sizeof(double) * MAXK, 256);
+  w.alpha_off = off;
+  off += align_up(s * (size_t)k * (deg + 1), 256);
+  w.beta_off = off;
+  off += align_up(s * (size_t)k * (deg + 1), 256);
+  w.steps_off = off;
+  off += align_up(sizeof(int32_t) * MAXK, 256);
+  w.xn_off = off;
+  off += align_up(sizeof(double) * MAXK, 256);
+  w.coef_off = off;
+  off += align_up(sizeof(double) * (size_t)k * deg, 256);
+  w.theta_off = off;
+  off += align_up(sizeof(double) * (size_t)k * deg, 256);
+  w.tau_off = off;
+  off += align_up(sizeof(double) * (size_t)k * deg, 256);
+  w.scr_off = off;
+  off += align_up(sizeof(double) * ((size_t)deg * deg + deg) * k, 256);
+  w.info_off = off;
+  off += align_up(sizeof(int32_t) * MAXK, 256);
+  w.total = off;
+  return w;
+}
+}  // namespace
+
+size_t slq_replay_workspace_bytes(int64_t n, int k, int deg, int dtype) {
+  if (n <= 0 || k <= 0 || deg <= 0) return 0;
+  return replay_layout(n, k, deg, dtype).total;
+}
+
+int slq_lanczos_replay(slq_op* op, const void* X_dev, int k, int deg, const void* alpha_dev, const void* beta_dev,
+                       const int32_t* steps_dev, const double* xnorm2_dev, const double* coeffs_dev, void* Y_dev, void* workspace_dev,
+                       size_t workspace_bytes, slq_stream stream) {
+  SLQ_REQUIRE(op && X_dev && alpha_dev && beta_dev && steps_dev && xnorm2_dev && coeffs_dev && Y_dev && workspace_dev, "NULL argument");
+  SLQ_REQUIRE(deg > 0, "Number of steps must be positive!");
+  SLQ_REQUIRE(is_pow2(k) && k <= MAXK, "block width k=%d must be a power of two in [1,64]", k);
+  SLQ_REQUIRE(X_dev != Y_dev, "X and Y must not alias");
+  SLQ_REQUIRE((((uintptr_t)X_dev | (uintptr_t)Y_dev) & 31) == 0 && ((uintptr_t)workspace_dev & 255) == 0,
+              "X and Y must be 32-byte and workspace 256-byte aligned");
+  if (sm_count() <= 0) return fail(SLQ_ERR_CUDA, "no CUDA device");
+  const ReplayWs w = replay_layout(op->n, k, deg, op->dtype);
+  SLQ_REQUIRE(workspace_bytes >= w.total, "workspace too small: %zu < %zu", workspace_bytes, w.total);
+  char* base = (char*)workspace_dev;
+  double* table = (double*)(base + w.table_off);
+  double* y0 = (double*)(base + w.y0_off);
+  cudaStream_t st = (cudaStream_t)stream;
+  return op->dtype == SLQ_F64
+             ? replay_dispatch<double>(op, X_dev, k, deg, alpha_dev, beta_dev, steps_dev, xnorm2_dev, coeffs_dev, Y_dev, table, y0, base,
+                                       base + w.panel, base + 2 * w.panel, st)
+             : replay_dispatch<float>(op, X_dev, k, deg, alpha_dev, beta_dev, steps_dev, xnorm2_dev, coeffs_dev, Y_dev, table, y0, base,
+                                      base + w.panel, base + 2 * w.panel, st);
+}
+
+size_t slq_funm_workspace_bytes(int64_t n, int k, int deg, int dtype) {
+  if (n <= 0 || k <= 0 || deg <= 0) return 0;
+  return funm_layout(n, k, deg, dtype).total;
+}
+
+int slq_funm_matmat(slq_op* op, const void* X_dev, int k, int deg, double rtol, int fun, const double* params, void* Y_dev,
+                    void* workspace_dev, size_t workspace_bytes, slq_stream stream) {
+  SLQ_REQUIRE(op && X_dev && Y_dev && workspace_dev, "NULL argument");
+  SLQ_REQUIRE(deg > 0, "Number of steps must be positive!");
+  SLQ_REQUIRE(is_pow2(k) && k <= MAXK, "block width k=%d must be a power of two in [1,64]", k);
+  SLQ_REQUIRE(X_dev != Y_dev, "X and Y must not alias");
+  SLQ_REQUIRE(fun >= SLQ_FUN_IDENTITY && fun <= SLQ_FUN_SOFTSIGN, "Unknown function: %d.", fun);
+  if (sm_count() <= 0) return fail(SLQ_ERR_CUDA, "no CUDA device");
+  const FunmWs w = funm_layout(op->n, k, deg, op->dtype);
+  SLQ_REQUIRE(workspace_bytes >= w.total, "workspace too small: %zu < %zu", workspace_bytes, w.total);
+  SLQ_REQUIRE(((uintptr_t)workspace_dev & 255) == 0, "workspace must be 256-byte aligned");
+  char* base = (char*)workspace_dev;
+  cudaStream_t st = (cudaStream_t)stream;
+  void* xcopy = base;
+  void* alpha = base + w.alpha_off;
+  void* beta = base + w.beta_off;
+  int32_t* steps = (int32_t*)(base + w.steps_off);
+  double* xn = (double*)(base + w.xn_off);
+  double* coeffs = (double*)(base + w.coef_off);
+  // pass 1: the orth = 0 recurrence on a copy of X (the driver clobbers its start block), keeping alpha / beta only
+  SLQ_CUDA(cudaMemcpyAsync(xcopy, X_dev, (size_t)op->n * k * dtype_size(op->dtype), cudaMemcpyDeviceToDevice, st));
+  int rc = slq_lanczos(op, xcopy, k, deg, rtol, 0, 2, alpha, beta, steps, xn, nullptr, base + w.lz_off,
+                       ws_layout(op->n, k, 2, op->dtype, nullptr, nullptr), stream);
+  if (rc != SLQ_OK) return rc;
+  // c = Y f(Theta) Y^T e_1 per probe (operators.py:122-124)
+  rc = slq_funm_coeffs(alpha, beta, op->dtype, k, deg, deg + 1, fun, params, coeffs, (double*)(base + w.theta_off),
+                       (double*)(base + w.tau_off), (double*)(base + w.scr_off), (int32_t*)(base + w.info_off), stream);
+  if (rc != SLQ_OK) return rc;
+  // pass 2: the same recurrence from the intact X with the recorded coefficients, Y accumulated on the fly
+  double* table = (double*)(base + w.table_off);
+  double* y0 = (double*)(base + w.y0_off);
+  char* lzp = base + w.lz_off;  // ws_layout places the panels first
+  return op->dtype == SLQ_F64
+             ? replay_dispatch<double>(op, X_dev, k, deg, alpha, beta, steps, xn, coeffs, Y_dev, table, y0, xcopy, lzp, lzp + w.panel, st)
+             : replay_dispatch<float>(op, X_dev, k, deg, alpha, beta, steps, xn, coeffs, Y_dev, table, y0, xcopy, lzp, lzp + w.panel, st);
+}
+
 int slq_block_from_columns(const void* cols_dev, int64_t n, int k, int dtype, void* X_dev, slq_stream stream) {
   SLQ_REQUIRE(cols_dev && X_dev && n > 0 && k > 0, "invalid argument");
   if (sm_count() <= 0) return fail(SLQ_ERR_CUDA, "no CUDA device");

@@ -72,5 +72,9 @@ int lanczos_dispatch(slq_op* op, void* X, int k, int deg, double rtol, int orth,
                      double* xnorm2, void* Q, char* ws, cudaStream_t st);
 template <typename T>
 int matmat_dispatch(slq_op* op, const void* X, void* Y, int k, cudaStream_t st);
+template <typename T>
+int replay_dispatch(slq_op* op, const void* X, int k, int deg, const void* alpha, const void* beta, const int32_t* steps,
+                    const double* xnorm2, const double* coeffs, void* Y, double* table, double* y0, void* P0, void* P1, void* P2,
+                    cudaStream_t st);
 
 }  // namespace slq

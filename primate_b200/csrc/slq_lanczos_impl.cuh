@@ -305,7 +305,17 @@ __device__ __forceinline__ void chunk_gather(T (&acc)[V], const RowChunk<T, CsrT
   }
 }
 
-enum StepMode { STEP_FIRST = 0, STEP_NEXT = 1, STEP_PLAIN = 2 };  // PLAIN: w = A u_c only (slq_op_matmat)
+// PLAIN: w = A u_c only (slq_op_matmat).  REPLAY: the whole Lanczos step with RECORDED alpha/beta (second pass of the
+// basis-free f(A) X): v = (A u_c) r_c - beta r_p u_p - alpha r_c u_c and Y += c_{j+1} ||x|| r_n v in one kernel.
+enum StepMode { STEP_FIRST = 0, STEP_NEXT = 1, STEP_PLAIN = 2, STEP_REPLAY = 3 };
+
+// Per-step scalars of the replay (one row of the table built by k_replay_table): rc | brp | cf | yc, MAXK doubles each.
+struct ReplayArgs {
+  const double* row = nullptr;
+  const double* y0 = nullptr;  // coefficient of the start vector (read when first != 0)
+  void* Y = nullptr;           // n x K accumulator panel
+  int first = 0;
+};
 
 // ---- kernel A (CSR operators): w = (A u_c) r_c - beta_j (u_p r_p); alpha partials ------------------------------------
 template <typename T, int K, int MODE>
@@ -1011,6 +1021,145 @@ static int lanczos_impl(slq_op* op, T* X, int deg, double rtol, int orth, int nc
   return SLQ_OK;
 }
 
+// ---- basis-free f(A) X: second ("replay") pass ---------------------------------------------------------------------
+// Table of the per-step, per-probe scalars of a recorded Lanczos run, in exactly the roundings the first pass used
+// (finalize<>: FIN_INIT / FIN_ALPHA / FIN_BETA), so that the replayed vectors are bit-identical to the first pass':
+//   row j:  rc  = scale of u_j            (1/||x|| for j = 0, 1/beta_j after)
+//           brp = beta_j * scale of u_{j-1}
+//           cf  = alpha_j * rc
+//           yc  = c_{j+1} ||x|| * scale of u_{j+1}   (0 when vector j+1 does not exist: early break, lanczos.h:140)
+//   y0 = c_0 ||x|| * scale of u_0.   Steps a probe never executed get all-zero scalars: its vectors stay 0.
+template <typename T>
+__global__ void k_replay_table(const T* __restrict__ alpha, const T* __restrict__ beta, int ld, int deg, int k,
+                               const int32_t* __restrict__ steps, const double* __restrict__ xnorm2, const double* __restrict__ coeffs,
+                               double* __restrict__ table, double* __restrict__ y0) {
+  const int j = blockIdx.x, t = threadIdx.x;
+  if (t >= MAXK) return;
+  double* row = table + (size_t)j * 4 * MAXK;
+  if (t >= k) {
+    row[t] = row[MAXK + t] = row[2 * MAXK + t] = row[3 * MAXK + t] = 0.0;
+    if (j == 0) y0[t] = 0.0;
+    return;
+  }
+  const double z = xnorm2[t];
+  const int nst = steps[t];
+  auto scale_of = [&](int m) -> double {  // reciprocal scale of the un-normalised Lanczos vector u_m
+    if (m == 0) return (z > 0.0) ? round_to<T>(1.0 / round_to<T>(sqrt(round_to<T>(z)))) : 1.0;
+    return round_to<T>(1.0 / (double)beta[(size_t)t * ld + m]);
+  };
+  const double xn = sqrt(z);
+  if (j == 0) y0[t] = coeffs[(size_t)t * deg] * xn * scale_of(0);
+  if (j >= nst) {
+    row[t] = row[MAXK + t] = row[2 * MAXK + t] = row[3 * MAXK + t] = 0.0;
+    return;
+  }
+  const double rc = scale_of(j);
+  row[t] = rc;
+  row[MAXK + t] = (j == 0) ? 0.0 : (double)((T)beta[(size_t)t * ld + j] * (T)scale_of(j - 1));
+  row[2 * MAXK + t] = round_to<T>((double)alpha[(size_t)t * ld + j] * rc);
+  row[3 * MAXK + t] = (j + 1 < deg && j + 1 < nst) ? coeffs[(size_t)t * deg + j + 1] * xn * scale_of(j + 1) : 0.0;
+}
+
+// Generic replay step (operators without the fused kernel: dense, callback, narrow or unaligned CSR): `w` holds A u_c on
+// entry (the operator's product); v and Y are formed in the arithmetic of k_stepA<.., FUSED_CSR = false> + k_axpy.
+template <typename T, int K>
+__global__ void __launch_bounds__(NT) k_replay_axpy(int64_t n, T* __restrict__ w, const T* __restrict__ uc, const T* __restrict__ up,
+                                                     T* __restrict__ Y, ReplayArgs rp) {
+  using M = BlockMap<T, K>;
+  constexpr int V = M::V, LPR = M::LPR;
+  const int slot = (threadIdx.x % LPR) * V;
+  T rc[V], brp[V], cf[V], yc[V], y0[V];
+#pragma unroll
+  for (int i = 0; i < V; ++i) {
+    rc[i] = (T)rp.row[slot + i];
+    brp[i] = (T)rp.row[MAXK + slot + i];
+    cf[i] = (T)rp.row[2 * MAXK + slot + i];
+    yc[i] = (T)rp.row[3 * MAXK + slot + i];
+    y0[i] = rp.first ? (T)rp.y0[slot + i] : (T)0;
+  }
+  const int64_t nvec = n * LPR;
+  for (int64_t e = (int64_t)blockIdx.x * NT + threadIdx.x; e < nvec; e += (int64_t)gridDim.x * NT) {
+    Pack<T, V> wv = ld_pack<T, V, LD_STREAM>(w + e * V);
+    const Pack<T, V> qc = ld_pack<T, V, LD_DEFAULT>(uc + e * V);
+    Pack<T, V> pv, yv;
+    if (!rp.first) {
+      pv = ld_pack<T, V, LD_STREAM>(up + e * V);
+      yv = ld_pack<T, V, LD_STREAM>(Y + e * V);
+    }
+#pragma unroll
+    for (int q = 0; q < V; ++q) {
+      const T t1 = rp.first ? mul_rn(wv.v[q], rc[q]) : fnma_rn(brp[q], pv.v[q], mul_rn(wv.v[q], rc[q]));
+      wv.v[q] = fnma_rn(cf[q], qc.v[q], t1);
+      const T y_old = rp.first ? mul_rn(y0[q], qc.v[q]) : yv.v[q];
+      yv.v[q] = fma_rn(yc[q], wv.v[q], y_old);
+    }
+    st_pack<T, V, false>(w + e * V, wv);
+    st_pack<T, V, true>(Y + e * V, yv);
+  }
+}
+
+// Y = y0 * X (deg == 1: only the start vector contributes)
+template <typename T, int K>
+__global__ void __launch_bounds__(NT) k_replay_first_only(int64_t n, const T* __restrict__ x, T* __restrict__ Y, const double* y0) {
+  using M = BlockMap<T, K>;
+  constexpr int V = M::V, LPR = M::LPR;
+  const int slot = (threadIdx.x % LPR) * V;
+  const int64_t nvec = n * LPR;
+  for (int64_t e = (int64_t)blockIdx.x * NT + threadIdx.x; e < nvec; e += (int64_t)gridDim.x * NT) {
+    Pack<T, V> xv = ld_pack<T, V, LD_STREAM>(x + e * V);
+#pragma unroll
+    for (int q = 0; q < V; ++q) xv.v[q] = mul_rn((T)y0[slot + q], xv.v[q]);
+    st_pack<T, V, true>(Y + e * V, xv);
+  }
+}
+
+// Replays steps 0 .. deg-2 of the recorded run from the intact start block X, accumulating Y = sum_m c_m ||x|| q_m
+// (operators.py:124 without Q).  P0..P2: three scratch panels; `table`/`y0` from k_replay_table.
+template <typename T, int K>
+static int replay_impl(slq_op* op, const T* X, int deg, const double* table, const double* y0, T* Y, T* P0, T* P1, T* P2,
+                       cudaStream_t st) {
+  const int64_t n = op->n;
+  using M = BlockMap<T, K>;
+  const int g_vec = grid_for(n * M::LPR, NT * 4);
+  if (g_vec <= 0) return fail(SLQ_ERR_CUDA, "no CUDA device");
+  if (deg <= 1) {
+    k_replay_first_only<T, K><<<g_vec, NT, 0, st>>>(n, X, Y, y0);
+    SLQ_LAUNCH_CHECK();
+    return SLQ_OK;
+  }
+  T* P[3] = {P0, P1, P2};
+  bool fused = false;
+  if constexpr (tma_supported<T, K>()) {
+    fused = op->kind == OP_CSR && use_tma_path() &&
+            (((uintptr_t)op->colidx | (uintptr_t)op->vals | (uintptr_t)X | (uintptr_t)Y | (uintptr_t)P0 | (uintptr_t)P1 | (uintptr_t)P2) & 15) == 0;
+  }
+  StepOut so{};
+  for (int j = 0; j + 1 < deg; ++j) {
+    const T* uc = (j == 0) ? X : P[(j - 1) % 3];
+    const T* up = (j <= 1) ? X : P[(j - 2) % 3];  // unused at j = 0 (brp = 0): any finite panel
+    T* w = P[j % 3];
+    ReplayArgs rp;
+    rp.row = table + (size_t)j * 4 * MAXK;
+    rp.y0 = y0;
+    rp.Y = Y;
+    rp.first = (j == 0);
+    const int pslot = prof_begin(PROF_STEPA, st);
+    if (fused) {
+      if constexpr (tma_supported<T, K>()) {
+        int rc = launch_stepA_tma<T, K, STEP_REPLAY>(op, uc, up, w, nullptr, nullptr, nullptr, nullptr, so, st, rp);
+        if (rc != SLQ_OK) return rc;
+      }
+    } else {
+      int rc = op_apply<T, K>(op, uc, w, st);
+      if (rc != SLQ_OK) return rc;
+      k_replay_axpy<T, K><<<g_vec, NT, 0, st>>>(n, w, uc, up, Y, rp);
+      SLQ_LAUNCH_CHECK();
+    }
+    prof_end(PROF_STEPA, pslot, st);
+  }
+  return SLQ_OK;
+}
+
 #define SLQ_DISPATCH_K(T, k, CALL)                        \
   switch (k) {                                            \
     case 1: { constexpr int KK = 1; return CALL; }        \
@@ -1032,6 +1181,15 @@ int lanczos_dispatch(slq_op* op, void* X, int k, int deg, double rtol, int orth,
 template <typename T>
 int matmat_dispatch(slq_op* op, const void* X, void* Y, int k, cudaStream_t st) {
   SLQ_DISPATCH_K(T, k, (op_apply<T, KK>(op, (const T*)X, (T*)Y, st)));
+}
+
+template <typename T>
+int replay_dispatch(slq_op* op, const void* X, int k, int deg, const void* alpha, const void* beta, const int32_t* steps,
+                    const double* xnorm2, const double* coeffs, void* Y, double* table, double* y0, void* P0, void* P1, void* P2,
+                    cudaStream_t st) {
+  k_replay_table<T><<<deg, MAXK, 0, st>>>((const T*)alpha, (const T*)beta, deg + 1, deg, k, steps, xnorm2, coeffs, table, y0);
+  SLQ_LAUNCH_CHECK();
+  SLQ_DISPATCH_K(T, k, (replay_impl<T, KK>(op, (const T*)X, deg, table, y0, (T*)Y, (T*)P0, (T*)P1, (T*)P2, st)));
 }
 
 

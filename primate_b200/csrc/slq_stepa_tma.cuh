@@ -178,13 +178,13 @@ template <typename T, int K, int MODE, bool LONGROWS>
 __global__ void __launch_bounds__(TmaTiling<T, K, LONGROWS>::NTHREADS, 1)
     k_stepA_tma(int n, const int32_t* __restrict__ rowptr, const int32_t* __restrict__ colidx, const T* __restrict__ vals,
                 const T* __restrict__ uc, const T* __restrict__ up, T* __restrict__ w, LzScal* sc, const double* scale_c,
-                const double* scale_p, double* partial, StepOut so) {
+                const double* scale_p, double* partial, StepOut so, ReplayArgs rp) {
   using C = TmaTiling<T, K, LONGROWS>;
   constexpr int V = C::V, LPR = C::LPR, RPP = C::RPP, PASSES = C::PASSES, TILE = C::TILE, CAP = C::CAP;
   constexpr int STAGES = LONGROWS ? C::BAL_STAGES : C::STAGES;  // the balanced variant gives stages up for the row accumulators
   constexpr int UB = SLQ_TMA_UB;
   constexpr int U = SLQ_TMA_U, R = C::R;
-  constexpr bool FIRST = (MODE == STEP_FIRST), PLAIN = (MODE == STEP_PLAIN);
+  constexpr bool FIRST = (MODE == STEP_FIRST), PLAIN = (MODE == STEP_PLAIN), REPLAY = (MODE == STEP_REPLAY);
   constexpr bool HAS_UP = !FIRST && !PLAIN;
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ uint64_t bar_full[STAGES], bar_empty[STAGES];
@@ -194,6 +194,7 @@ __global__ void __launch_bounds__(TmaTiling<T, K, LONGROWS>::NTHREADS, 1)
   double* s_red = reinterpret_cast<double*>(s_scratch);  // alpha partials per consumer warp; re-used by the finaliser
   T* s_part = reinterpret_cast<T*>(s_scratch);           // long rows: one partial probe-row per row group
   __shared__ T s_rc[K], s_brp[K];
+  __shared__ T s_cf[REPLAY ? K : 1], s_yc[REPLAY ? K : 1], s_y0[REPLAY ? K : 1];  // replay: alpha_j r_c, Y coefficients
 
   unsigned char* const base = smem_raw;  // bulk copies need 16-byte alignment only
   T* const s_acc = reinterpret_cast<T*>(smem_raw + (size_t)STAGES * C::STAGE_BYTES);  // balanced variant: TILE x K row sums
@@ -211,7 +212,16 @@ __global__ void __launch_bounds__(TmaTiling<T, K, LONGROWS>::NTHREADS, 1)
   if (LONGROWS) {
     for (int t = tid; t < TILE * K; t += C::NTHREADS) s_acc[t] = (T)0;
   }
-  if (!PLAIN) {
+  if (REPLAY) {
+    // recorded recurrence: every per-probe scalar of this step comes from the replay table (no grid-wide reductions)
+    for (int t = tid; t < K; t += C::NTHREADS) {
+      s_rc[t] = (T)rp.row[t];
+      s_brp[t] = (T)rp.row[MAXK + t];
+      s_cf[REPLAY ? t : 0] = (T)rp.row[2 * MAXK + t];
+      s_yc[REPLAY ? t : 0] = (T)rp.row[3 * MAXK + t];
+      s_y0[REPLAY ? t : 0] = rp.first ? (T)rp.y0[t] : (T)0;
+    }
+  } else if (!PLAIN) {
     for (int t = tid; t < K; t += C::NTHREADS) {
       s_rc[t] = (T)scale_c[t];
       s_brp[t] = FIRST ? (T)0 : (T)(sc->beta[t]) * (T)scale_p[t];
@@ -330,8 +340,8 @@ __global__ void __launch_bounds__(TmaTiling<T, K, LONGROWS>::NTHREADS, 1)
     T rc_r[V], brp_r[V];
 #pragma unroll
     for (int q = 0; q < V; ++q) {
-      rc_r[q] = (PLAIN || HOIST < 2) ? (T)1 : s_rc[slot + q];
-      brp_r[q] = (PLAIN || HOIST < 1) ? (T)0 : s_brp[slot + q];
+      rc_r[q] = (PLAIN || REPLAY || HOIST < 2) ? (T)1 : s_rc[slot + q];
+      brp_r[q] = (PLAIN || REPLAY || HOIST < 1) ? (T)0 : s_brp[slot + q];
     }
     if constexpr (!LONGROWS) {
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
@@ -387,14 +397,29 @@ __global__ void __launch_bounds__(TmaTiling<T, K, LONGROWS>::NTHREADS, 1)
                   Pack<T, V> pv;
                   if (HAS_UP) pv = *reinterpret_cast<const Pack<T, V>*>(s_up + (size_t)rl * K + slot);
                   const Pack<T, V> qcr = *reinterpret_cast<const Pack<T, V>*>(s_uc + (size_t)rl * K + slot);
+                  if constexpr (REPLAY) {
+                    // v = (A u_c) r_c - beta_j r_p u_p - alpha_j r_c u_c in the arithmetic of step A + axpy;  Y += yc v
+                    Pack<T, V> yv;
+                    if (!rp.first) yv = ld_pack<T, V, LD_STREAM>(reinterpret_cast<const T*>(rp.Y) + off);
+#pragma unroll
+                    for (int q = 0; q < V; ++q) {
+                      const T t1 = fnma_rn(s_brp[slot + q], pv.v[q], mul_rn(a2[r][q], s_rc[slot + q]));
+                      wv.v[q] = fnma_rn(s_cf[slot + q], qcr.v[q], t1);
+                      const T y_old = rp.first ? mul_rn(s_y0[slot + q], qcr.v[q]) : yv.v[q];
+                      yv.v[q] = fma_rn(s_yc[slot + q], wv.v[q], y_old);
+                    }
+                    st_pack<T, V, false>(w + off, wv);
+                    st_pack<T, V, true>(reinterpret_cast<T*>(rp.Y) + off, yv);
+                  } else {
 #pragma unroll
                   for (int q = 0; q < V; ++q) {
                     const T rcq = HOIST >= 2 ? rc_r[q] : s_rc[slot + q];
                     const T brq = HOIST >= 1 ? brp_r[q] : s_brp[slot + q];
-                    wv.v[q] = FIRST ? a2[r][q] * rcq : a2[r][q] * rcq - brq * pv.v[q];
+                    wv.v[q] = FIRST ? mul_rn(a2[r][q], rcq) : fnma_rn(brq, pv.v[q], mul_rn(a2[r][q], rcq));
                     acc_a[q] += (double)(qcr.v[q] * rcq) * (double)wv.v[q];
                   }
                   st_pack<T, V, false>(w + off, wv);
+                  }
                 }
               }
             }
@@ -521,14 +546,28 @@ __global__ void __launch_bounds__(TmaTiling<T, K, LONGROWS>::NTHREADS, 1)
                 Pack<T, V> pv;
                 if (HAS_UP) pv = *reinterpret_cast<const Pack<T, V>*>(s_up + (size_t)rl * K + slot);
                 const Pack<T, V> qcr = *reinterpret_cast<const Pack<T, V>*>(s_uc + (size_t)rl * K + slot);
+                if constexpr (REPLAY) {
+                  Pack<T, V> yv;
+                  if (!rp.first) yv = ld_pack<T, V, LD_STREAM>(reinterpret_cast<const T*>(rp.Y) + off);
+#pragma unroll
+                  for (int q = 0; q < V; ++q) {
+                    const T t1 = fnma_rn(s_brp[slot + q], pv.v[q], mul_rn(av.v[q], s_rc[slot + q]));
+                    wv.v[q] = fnma_rn(s_cf[slot + q], qcr.v[q], t1);
+                    const T y_old = rp.first ? mul_rn(s_y0[slot + q], qcr.v[q]) : yv.v[q];
+                    yv.v[q] = fma_rn(s_yc[slot + q], wv.v[q], y_old);
+                  }
+                  st_pack<T, V, false>(w + off, wv);
+                  st_pack<T, V, true>(reinterpret_cast<T*>(rp.Y) + off, yv);
+                } else {
 #pragma unroll
                 for (int q = 0; q < V; ++q) {
                   const T rcq = HOIST >= 2 ? rc_r[q] : s_rc[slot + q];
                   const T brq = HOIST >= 1 ? brp_r[q] : s_brp[slot + q];
-                  wv.v[q] = FIRST ? av.v[q] * rcq : av.v[q] * rcq - brq * pv.v[q];
+                  wv.v[q] = FIRST ? mul_rn(av.v[q], rcq) : fnma_rn(brq, pv.v[q], mul_rn(av.v[q], rcq));
                   acc_a[q] += (double)(qcr.v[q] * rcq) * (double)wv.v[q];
                 }
                 st_pack<T, V, false>(w + off, wv);
+                }
               }
             }
           }
@@ -545,7 +584,7 @@ __global__ void __launch_bounds__(TmaTiling<T, K, LONGROWS>::NTHREADS, 1)
     }
   }
 
-  if (!PLAIN) {
+  if (!PLAIN && !REPLAY) {
     // deterministic CTA reduction of the alpha partials: row groups inside a warp by shuffles, warps through shared memory
     if (warp < C::CW) {
 #pragma unroll
@@ -573,7 +612,7 @@ __global__ void __launch_bounds__(TmaTiling<T, K, LONGROWS>::NTHREADS, 1)
 
 template <typename T, int K, int MODE>
 static int launch_stepA_tma(const slq_op* op, const T* uc, const T* up, T* w, LzScal* sc, const double* scale_c, const double* scale_p,
-                            double* partial, const StepOut& so, cudaStream_t st) {
+                            double* partial, const StepOut& so, cudaStream_t st, const ReplayArgs& rp = ReplayArgs{}) {
   using C = TmaTiling<T, K>;
   using CB = TmaTiling<T, K, true>;
   static DeviceOnce once;  // per (T, K, MODE) instantiation, tracked per device
@@ -587,10 +626,10 @@ static int launch_stepA_tma(const slq_op* op, const T* uc, const T* up, T* w, Lz
   const int g = ntiles < sm_count() ? ntiles : sm_count();
   if (op->max_row_nnz > C::LONG)
     k_stepA_tma<T, K, MODE, true><<<g, C::NTHREADS, CB::SMEM_BAL, st>>>(n, op->rowptr, op->colidx, (const T*)op->vals, uc, up, w, sc,
-                                                                         scale_c, scale_p, partial, so);
+                                                                         scale_c, scale_p, partial, so, rp);
   else
     k_stepA_tma<T, K, MODE, false><<<g, C::NTHREADS, C::SMEM_BYTES, st>>>(n, op->rowptr, op->colidx, (const T*)op->vals, uc, up, w, sc,
-                                                                          scale_c, scale_p, partial, so);
+                                                                          scale_c, scale_p, partial, so, rp);
   SLQ_LAUNCH_CHECK();
   return SLQ_OK;
 }

@@ -378,6 +378,43 @@ class DeviceOperator:
 		return {"alpha": alpha, "beta": beta, "steps": steps, "xnorm2": xnorm2, "Q": Q}
 
 
+	def _scratch(self, key, nbytes: int):
+		"""256-byte aligned device scratch of at least `nbytes`, cached under `key` (only the latest shape is kept)."""
+		if key not in self._ws:
+			self._ws = {key: _torch().empty(nbytes + 256, dtype=_torch().uint8, device="cuda")}
+		buf = self._ws[key]
+		off = (-buf.data_ptr()) % 256
+		return buf.data_ptr() + off, buf.numel() - off
+
+	def funm_matmat(self, X, deg: int, rtol: float, fun_id: int, params):
+		"""Y = f(A) X for a device probe block X (n, k) in the CALLER's row order, left intact: the basis-free two-pass
+		Lanczos engine (libslq: slq_funm_matmat; orth = 0, built-in f).  Five panels of memory whatever `deg` is."""
+		torch = _torch()
+		L = _ffi.lib()
+		n, k = int(X.shape[0]), int(X.shape[1])
+		assert n == self.n and X.is_contiguous() and X.dtype == _tdtype(self.dtype)
+		Xi = self._to_internal(X)
+		Y = torch.empty_like(Xi)
+		ws_ptr, ws_bytes = self._scratch(("funm", k, int(deg)), L.slq_funm_workspace_bytes(self.n, k, int(deg), self.code))
+		self._check(L.slq_funm_matmat(self._handle, Xi.data_ptr(), k, int(deg), float(rtol), int(fun_id), params, Y.data_ptr(), ws_ptr,
+		                              ws_bytes, _stream_ptr()))  # fmt: skip
+		return self._from_internal(Y)
+
+	def lanczos_replay(self, X, deg: int, run: dict, coeffs):
+		"""Second pass of the two-pass engine with caller-provided Krylov coefficients `coeffs` (k, deg) float64 device
+		tensor: `run` is what `lanczos(copy of X, deg, rtol, orth=0, ncv=2)` returned for the same start block."""
+		torch = _torch()
+		L = _ffi.lib()
+		n, k = int(X.shape[0]), int(X.shape[1])
+		Xi = self._to_internal(X)
+		Y = torch.empty_like(Xi)
+		ws_ptr, ws_bytes = self._scratch(("replay", k, int(deg)), L.slq_replay_workspace_bytes(self.n, k, int(deg), self.code))
+		self._check(L.slq_lanczos_replay(self._handle, Xi.data_ptr(), k, int(deg), run["alpha"].data_ptr(), run["beta"].data_ptr(),
+		                                 run["steps"].data_ptr(), run["xnorm2"].data_ptr(), coeffs.contiguous().data_ptr(), Y.data_ptr(),
+		                                 ws_ptr, ws_bytes, _stream_ptr()))  # fmt: skip
+		return self._from_internal(Y)
+
+
 def fun_spec(fun, kwargs: Optional[dict] = None):
 	"""(fun_id, params) of a built-in spectral function name (special.py:78-107), or None for a Python callable."""
 	kw = dict(kwargs or {})

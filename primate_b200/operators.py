@@ -19,6 +19,7 @@ from .special import param_callable
 from .tridiag import eigh_tridiag  # noqa: F401
 
 F64: np.dtype = np.dtype("float64")
+_FORCE_STORED_BASIS = False  # tests / A-B timing: route orth = 0 through the stored-basis formula too
 
 
 def _op_checks(A: Any) -> list:
@@ -143,24 +144,39 @@ class MatrixFunction(LinearOperator):
 		_, _, y, _ = engine.quadrature(alpha, beta, self._deg, fid, prm, scale=xnorm2, want_nodes=False)
 		return y
 
-	def matmat_block(self, X):
-		"""f(A) X for a device probe block X (n, k) (clobbered) -> device block (n, k)."""
+	def _host_coeffs(self, out):
+		"""Krylov coefficients c = Y f(Theta) Y^T e_1 for a Python callable: eigenvectors from the device QL solver, `f`
+		evaluated on the host on the (k x deg) Ritz values (operators.py:122-124)."""
 		torch = engine._torch()
+		_, theta, _, scratch, _ = engine.funm_coeffs(out["alpha"], out["beta"], self._deg, fun_id=-1)
+		k, m = theta.shape
+		th, sc = theta.cpu().numpy(), scratch.cpu().numpy()
+		Zt = sc[: k * m * m].reshape(k, m, m)
+		perm = sc[k * m * m :].reshape(k, m).astype(np.int64)
+		C = np.empty((k, m))
+		for p in range(k):
+			Y = Zt[p][perm[p], :].T  # (m, m), columns sorted like theta
+			C[p] = Y @ (np.ravel(self._fun(th[p])) * Y[0, :])
+		return torch.from_numpy(C).cuda()
+
+	def matmat_block(self, X):
+		"""f(A) X for a device probe block X (n, k) -> device block (n, k).
+
+		orth = 0: the basis-free two-pass engine (X is left intact; memory independent of `deg`).  orth > 0: the
+		reference's stored-basis formula y = ||x|| Q Y f(Theta) Y^T e_1 (operators.py:102-124; X is clobbered)."""
+		torch = engine._torch()
+		if self._orth == 0 and not _FORCE_STORED_BASIS:
+			if self._fun_spec is not None:
+				fid, prm = self._fun_spec
+				return self.device_op.funm_matmat(X, self._deg, self._rtol, fid, prm)
+			run = self.device_op.lanczos(X.clone(), self._deg, self._rtol, 0, 2)
+			return self.device_op.lanczos_replay(X, self._deg, run, self._host_coeffs(run))
 		out = self.device_op.lanczos(X, self._deg, self._rtol, self._orth, self._deg, want_basis=True, internal_basis=True)
 		if self._fun_spec is not None:
 			fid, prm = self._fun_spec
 			coeffs, _, _, _, _ = engine.funm_coeffs(out["alpha"], out["beta"], self._deg, fid, prm)
 		else:
-			_, theta, _, scratch, _ = engine.funm_coeffs(out["alpha"], out["beta"], self._deg, fun_id=-1)
-			k, m = theta.shape
-			th, sc = theta.cpu().numpy(), scratch.cpu().numpy()
-			Zt = sc[: k * m * m].reshape(k, m, m)
-			perm = sc[k * m * m :].reshape(k, m).astype(np.int64)
-			C = np.empty((k, m))
-			for p in range(k):
-				Y = Zt[p][perm[p], :].T  # (m, m), columns sorted like theta
-				C[p] = Y @ (np.ravel(self._fun(th[p])) * Y[0, :])
-			coeffs = torch.from_numpy(C).cuda()
+			coeffs = self._host_coeffs(out)
 		Y = torch.empty_like(X)
 		from . import _ffi
 
@@ -170,8 +186,10 @@ class MatrixFunction(LinearOperator):
 
 	# ---- device-panel API (block drivers that keep their panels on the GPU) -----------------------------------------
 	def _basis_block_width(self, n: int, budget: int = 40 << 30) -> int:
-		"""Widest probe block (power of two <= 32) whose stored Lanczos basis (deg x n x k) stays within `budget` bytes."""
-		per_column = self._deg * n * np.dtype(self.dtype).itemsize
+		"""Widest probe block (power of two <= 32) for f(A) X: the two-pass engine (orth = 0) holds five panels whatever
+		`deg` is; the stored-basis path (orth > 0) is narrowed until its deg x n x k basis stays within `budget` bytes."""
+		itemsize = np.dtype(self.dtype).itemsize
+		per_column = (5 if (self._orth == 0 and not _FORCE_STORED_BASIS) else self._deg) * n * itemsize
 		k = 32
 		while k > 1 and k * per_column > budget:
 			k >>= 1
