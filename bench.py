@@ -4,19 +4,22 @@
   python bench.py --impl reference [--gpus N] [--steps K] ...     # the reference's own CPU code on the host cores
 
 Workload (BASELINE.json configs[1], SURVEY 8d "C2"): 5-point Laplacian on a 1000x1000 grid (n = 1e6, CSR fp64 /
-int32, 63.95 MB), f = log, deg = 50, orth = 0, Rademacher probes.  One STEP = one hutch pass over `--probes`
-(default 10 000) probes PER RANK, i.e. the whole C2 job per step per GPU ("weak" scaling: rank r of step s owns the
-probe indices [(s*N + r)*P, (s*N + r + 1)*P) of ONE PCG64 stream; the only collective is one all-gather of each
-rank's (count, mean, M2) record per step).  1 probe-step = one Lanczos iteration of one probe (lanczos.h:123-148).
+int32, 63.95 MB), f = log, deg = 50, orth = 0, Rademacher probes.  One STEP = one hutch pass over the WHOLE job of
+`--probes` (default 10 000) probes, sharded over the N ranks -- STRONG scaling, the north-star's ">= 7x at 8 GPUs" is
+about this job: in step s rank r owns the probe indices s*P + probe_range(P, r, N) of ONE PCG64 stream (device
+jump-ahead, no communication) and the only collective is one all-gather of each rank's (count, mean, M2) record per
+step.  1 probe-step = one Lanczos iteration of one probe (lanczos.h:123-148).  For N > 1 a `weak` sub-dict carries the
+round-1 reading as well (P probes PER RANK per step).
 
   value   device-resident throughput: operator and probe generator state already in HBM, timed with CUDA events;
   e2e     the same metric through the public API with HOST buffers: every step builds a MatrixFunction from the
-          host SciPy CSR matrix (pinned arrays -> H2D upload inside the timed region), runs
+          host SciPy CSR matrix (pinned arrays -> H2D upload inside the timed region, on every rank), runs
           hutch(M, converge="count", count=P) and reads the estimate back;
   roofline   dominant kernel (fused CSR SpMM + three-term recurrence, "step A"): algorithmic bytes per launch /
           its average duration measured with CUDA events on the launching stream inside the timed region;
   cpu_baseline  the reference's compiled extension (oracle/_ref) driven exactly as hutch drives it, on a bounded
-          sample of the same workload on the host cores (N = 1 only).
+          sample of the same workload on the host cores (N = 1 only);
+  configs  (N = 1) the other BASELINE configs at stated sizes, each with its throughput and roofline fraction.
 
 Working set per block (3 panels of n x 64 fp64 = 1.5 GB + CSR 64 MB) is far larger than the 126 MB L2, so no L2
 flush is needed between timed iterations ("inputs larger than L2").
@@ -49,12 +52,15 @@ def parse_args():
 	ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
 	ap.add_argument("--grid", type=int, default=1000, help="Laplacian grid side (C2: 1000 -> n = 1e6)")
 	ap.add_argument("--deg", type=int, default=50)
-	ap.add_argument("--probes", type=int, default=10000, help="probes per rank per step (C2: 10 000)")
+	ap.add_argument("--probes", type=int, default=10000, help="probes per step, the whole job (C2: 10 000); sharded over the ranks")
 	ap.add_argument("--block", type=int, default=64, help="probes per device block (power of two <= 64)")
 	ap.add_argument("--cpu-probes", type=int, default=0, help="reference arm: probes per worker per step (0 = auto)")
 	ap.add_argument("--cpu-workers", type=int, default=0, help="reference arm: worker processes (0 = all host cores)")
 	ap.add_argument("--no-cpu-baseline", action="store_true")
 	ap.add_argument("--no-e2e", action="store_true")
+	ap.add_argument("--no-configs", action="store_true", help="skip the C1/C3/C4/C5 side measurements (N = 1)")
+	ap.add_argument("--no-weak", action="store_true", help="N > 1: skip the secondary weak-scaling pass")
+	ap.add_argument("--c3-scale", type=int, default=22, help="configs: R-MAT scale of the C3 side measurement (BASELINE: 24)")
 	return ap.parse_args()
 
 
@@ -69,7 +75,12 @@ def laplacian_2d(g: int):
 
 def workload_name(args) -> str:
 	return (f"C2: hutch logdet, 2-D 5-point Laplacian {args.grid}x{args.grid} (n={args.grid ** 2} CSR fp64/int32), "
-	        f"f=log, deg={args.deg}, orth=0, {args.probes} Rademacher probes per rank per step")  # fmt: skip
+	        f"f=log, deg={args.deg}, orth=0, {args.probes} Rademacher probes per step (the whole job, sharded over the ranks)")  # fmt: skip
+
+
+def config_of(args) -> dict:
+	"""The `config` object, identical in both arms (everything arm-specific goes to `details`)."""
+	return {"workload": workload_name(args), "grid": args.grid, "deg": args.deg, "probes_per_step": args.probes, "fun": "log"}
 
 
 # ---- clocks -----------------------------------------------------------------------------------------------------
@@ -191,9 +202,9 @@ def run_reference(args, emit: bool = True) -> dict:
 	          f"{args.steps} steps; single-core rate {probe_steps / core_seconds:.1f} probe-steps/s/core")  # fmt: skip
 	line = {
 		"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-		"warmup": args.warmup, "ms_per_step": 1e3 * t_total / args.steps, "higher_is_better": True, "scaling": "weak",
+		"warmup": args.warmup, "ms_per_step": 1e3 * t_total / args.steps, "higher_is_better": True, "scaling": "strong",
 		"vs_baseline": None, "dtype": "f64", "data": "synthetic",
-		"config": {"workload": workload_name(args), "timing": "host wall clock (CPU only)"},
+		"config": config_of(args), "details": {"timing": "host wall clock (CPU only)"},
 		"cpu_baseline": {"value": value, "unit": UNIT, "cores": workers, "kind": "reference", "sample": sample},
 		"e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
 		"gpu_launches": 0,
@@ -255,12 +266,16 @@ def run_ours(args) -> None:
 	_ = M.device_op  # ingest once (locality ordering + upload): `value` is measured with the operator resident in HBM
 	stream = ProbeStream(n, "rademacher", seed=0, dtype=np.float64)
 
-	def device_step(s: int):
-		"""One hutch pass over this rank's P probes, everything resident; returns the merged (count, mean, M2)."""
-		first = (s * world + rank) * P
-		y = M.quad_range(stream, first, P, kb)  # Lanczos blocks back to back, then ONE batched Golub-Welsch launch
+	lo, hi = sharding.probe_range(P, rank, world)  # this rank's share of the P-probe job (strong scaling)
+
+	def device_step(s: int, first=None, count=None):
+		"""One hutch pass over this rank's share of the step's probes, everything resident; merged (count, mean, M2)."""
+		first = s * P + lo if first is None else first
+		count = hi - lo if count is None else count
 		state = torch.zeros(3, dtype=torch.float64, device="cuda")
-		engine.stats_update(y, state)
+		if count > 0:
+			y = M.quad_range(stream, first, count, kb)  # Lanczos blocks back to back, then ONE batched Golub-Welsch launch
+			engine.stats_update(y, state)
 		recs = comm.all_gather(state)  # one tiny collective per convergence check (N > 1: NCCL over NVLink)
 		return sharding.merge_records([tuple(r) for r in recs])
 
@@ -300,8 +315,25 @@ def run_ours(args) -> None:
 	if world > 1:
 		dist.all_reduce(t, op=dist.ReduceOp.MAX)
 	ms = float(t.item())
-	total_probe_steps = world * P * deg * args.steps
+	total_probe_steps = P * deg * args.steps
 	value = total_probe_steps / (ms * 1e-3)
+
+	# ---- secondary: weak scaling (P probes PER RANK per step, the round-1 reading) ----------------------------------
+	weak = None
+	if world > 1 and not args.no_weak:
+		wsteps = max(1, min(args.steps, 2))
+		device_step(0, first=rank * P, count=P)
+		sync_all()
+		w0, w1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+		w0.record()
+		for s_ in range(wsteps):
+			device_step(0, first=((1 + s_) * world + rank) * P, count=P)
+		w1.record()
+		sync_all()
+		wt = torch.tensor([w0.elapsed_time(w1)], dtype=torch.float64, device="cuda")
+		dist.all_reduce(wt, op=dist.ReduceOp.MAX)
+		weak = {"scaling": "weak", "probes_per_rank_per_step": P, "steps": wsteps, "ms_per_step": float(wt.item()) / wsteps,
+		        "value": world * P * deg * wsteps / (float(wt.item()) * 1e-3), "unit": UNIT}  # fmt: skip
 
 	# ---- end-to-end through the public API with host buffers ----------------------------------------------------
 	e2e = None
@@ -314,8 +346,8 @@ def run_ours(args) -> None:
 			_lz._OP_CACHE.clear()  # no operator caching across steps: the upload is part of every step
 			Me = MatrixFunction(Ah, "log", deg=deg, orth=0)
 			rng = np.random.default_rng(0)
-			rng.bit_generator.advance(s * world * P * n)  # step s starts at probe s*N*P of the one stream
-			return hutch(Me, converge="count", count=world * P, seed=rng)  # sharded over the ranks by `comm="auto"`
+			rng.bit_generator.advance(s * P * n)  # step s starts at probe s*P of the one stream
+			return hutch(Me, converge="count", count=P, seed=rng)  # the P probes are sharded over the ranks by `comm="auto"`
 
 		for s in range(min(args.warmup, 1)):
 			e2e_step(s)
@@ -333,7 +365,7 @@ def run_ours(args) -> None:
 		if world > 1:
 			dist.all_reduce(ems, op=dist.ReduceOp.MAX)
 		e2e = {"value": total_probe_steps / (float(ems.item()) * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
-		       "d2h_bytes_per_step": int(8 * P if world == 1 else 24 * world), "ms_per_step": float(ems.item()) / args.steps,
+		       "d2h_bytes_per_step": int(8 * P if world == 1 else 24), "ms_per_step": float(ems.item()) / args.steps,
 		       "wall_ms_per_step": 1e3 * wall / args.steps, "estimate": float(est),
 		       "api": "hutch(MatrixFunction(A_host_csr, 'log', deg, orth=0), converge='count', count=P, seed=rng)"}  # fmt: skip
 
@@ -341,7 +373,7 @@ def run_ours(args) -> None:
 		if world > 1:
 			dist.destroy_process_group()
 		return
-	run_ours_report(args, world, ms, value, launches, clk, prof, e2e, rec, n, nnz)
+	run_ours_report(args, world, ms, value, launches, clk, prof, e2e, rec, n, nnz, hi - lo, weak)
 	if world > 1:
 		dist.destroy_process_group()
 
@@ -364,11 +396,11 @@ def ncu_traffic(key: str):
 		return None
 
 
-def run_ours_report(args, world, ms, value, launches, clk, prof, e2e, rec, n, nnz) -> None:
+def run_ours_report(args, world, ms, value, launches, clk, prof, e2e, rec, n, nnz, my_probes, weak) -> None:
 	from primate_b200 import engine
 
 	P, deg = args.probes, args.deg
-	blocks = engine.block_sizes(P, args.block)
+	blocks = engine.block_sizes(my_probes, args.block)  # rank 0's share of the job
 	csr_bytes = nnz * 12 + (n + 1) * 4
 	# step-A algorithmic bytes per launch: CSR once + read u_c + read u_p (absent at j = 0) + write w  
 	stepA_bytes = sum(deg * csr_bytes + (3 * deg - 1) * n * k * 8 for k in blocks) / (deg * len(blocks))
@@ -390,7 +422,7 @@ def run_ours_report(args, world, ms, value, launches, clk, prof, e2e, rec, n, nn
 		                "frac": (axpy_bytes / (avgB * 1e-3) / 1e9 / peak) if cB else None},
 	}  # fmt: skip
 	# whole fused Lanczos step against SURVEY 8(d)'s B_step = CSR/k + 6 n s per probe-step
-	bstep = sum(k * deg * (csr_bytes / k + 6 * n * 8) for k in blocks) / (P * deg)
+	bstep = sum(k * deg * (csr_bytes / k + 6 * n * 8) for k in blocks) / (my_probes * deg)
 	roofline["whole_step"] = {"algorithmic_bytes_per_probe_step": bstep, "achieved": bstep * (value / world) / 1e9,
 	                          "frac": bstep * (value / world) / 1e9 / peak}  # fmt: skip
 
@@ -406,17 +438,103 @@ def run_ours_report(args, world, ms, value, launches, clk, prof, e2e, rec, n, nn
 		except Exception as exc:  # noqa: BLE001  (the baseline is a reported extra; never fail the bench line over it)
 			cpu = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": f"failed: {exc!r}"}
 
+	configs = None
+	if world == 1 and not args.no_configs:
+		configs = run_side_configs(args, peak)
+
 	line = {
 		"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-		"ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-		"data": "synthetic",
-		"config": {"workload": workload_name(args), "block": args.block, "parallelism": f"probe-sharded x{world}",
-		           "l2_policy": "inputs larger than L2 (3 panels of n x block fp64 = 1.5 GB at block 64, + 64 MB CSR, vs 126 MB L2); no flush needed",
-		           "collective": "one all-gather of (count, mean, M2) per rank per step" if world > 1 else "none"},
+		"ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+		"data": "synthetic", "config": config_of(args),
+		"details": {"block": args.block, "parallelism": f"probes of one {P}-probe job sharded x{world} (strong scaling)",
+		            "probes_on_rank0": my_probes,
+		            "l2_policy": "inputs larger than L2 (3 panels of n x block fp64 = 1.5 GB at block 64, + 64 MB CSR, vs 126 MB L2); no flush needed",
+		            "collective": "one all-gather of (count, mean, M2) per rank per step" if world > 1 else "none"},
 		"e2e": e2e, "gpu_launches": int(launches), "clocks": clk, "roofline": roofline, "cpu_baseline": cpu,
 		"check": {"count": rec[0], "mean_logdet": rec[1], "std": float(np.sqrt(rec[2] / max(rec[0] - 1, 1)))},
 	}  # fmt: skip
+	if weak is not None:
+		line["weak"] = weak
+	if configs is not None:
+		line["configs"] = configs
 	print(json.dumps(line), flush=True)
+
+
+def run_side_configs(args, peak_hbm: float) -> dict:
+	"""BASELINE.json's other configs on this GPU, each at a stated size that finishes in well under a minute, through the
+	generators and checks of scripts/run_configs.py: throughput in probe-steps/s and the fraction of the roofline that
+	bounds the config (HBM bytes per probe-step `CSR/k + 6 n s` for the sparse ones; for the dense C4 the
+	fp64 matrix product, against cuBLAS DGEMM timed here on the same shape as the yardstick)."""
+	import types
+
+	import torch
+
+	from scripts import run_configs as rc
+
+	out = {}
+	a = types.SimpleNamespace(c3_scale=args.c3_scale, c3_probes=64, c3_reorder="balance", c4_n=32768, c5_grid=256, c5_small=48)
+
+	def guarded(name, fn):
+		t0 = time.perf_counter()
+		try:
+			res = fn()
+		except Exception as exc:  # noqa: BLE001  (a side measurement never fails the bench line)
+			res = {"error": repr(exc)}
+		res["wall_s"] = time.perf_counter() - t0
+		out[name] = res
+		torch.cuda.empty_cache()
+
+	def c1():
+		r = rc.c1(a)
+		return {"workload": "C1: hutch logdet, dense SPD 1000x1000, deg=20, 200 probes, fp64 (full size; launch-bound at this n)",
+		        "probe_steps_per_s": r["probe_steps_per_s"], "ok": r["ok"],
+		        "roofline": {"bound": "launch latency", "achieved": None, "peak": None, "frac": None}}  # fmt: skip
+
+	def c3():
+		r = rc.c3(a)
+		n, nnz = r["n"], r["nnz"]
+		bstep = (nnz * 8 + (n + 1) * 4) / 32 + 6 * n * 4
+		ach = bstep * r["probe_steps_per_s"] / 1e9
+		return {"workload": f"C3: tr exp(-tL), R-MAT scale {a.c3_scale} (n={n}, nnz={nnz}, max degree {r['max_degree']}), fp32, deg=30, {a.c3_probes} probes (BASELINE size: scale 24)",
+		        "probe_steps_per_s": r["probe_steps_per_s"], "ok": r["ok"],
+		        "roofline": {"bound": "hbm", "achieved": ach, "peak": peak_hbm, "unit": "GB/s", "frac": ach / peak_hbm,
+		                     "algorithmic_bytes_per_probe_step": bstep}}  # fmt: skip
+
+	def c4():
+		r = rc.c4(a)
+		n = r["n"]
+		flops = 2.0 * n * n  # per probe-step: the dense product dominates (re-orthogonalisation: 4 n j flops at step j)
+		A = torch.randn((n, n), device="cuda", dtype=torch.float64)
+		X = torch.randn((n, 32), device="cuda", dtype=torch.float64)
+		for _ in range(2):
+			torch.matmul(A, X)
+		e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+		e0.record()
+		for _ in range(5):
+			torch.matmul(A, X)
+		e1.record()
+		torch.cuda.synchronize()
+		dgemm_tf = 5 * 2.0 * n * n * 32 / (e0.elapsed_time(e1) * 1e-3) / 1e12
+		del A, X
+		ach = flops * r["probe_steps_per_s"] / 1e12
+		return {"workload": f"C4: numerical rank, dense Gram {n}x{n} (rank {r['rank']}), smoothstep, deg=100, orth=100, 64 probes, fp64 (full size)",
+		        "probe_steps_per_s": r["probe_steps_per_s"], "ok": r["ok"], "rank_estimate": r["mean"],
+		        "roofline": {"bound": "fp64 tensor (yardstick: cuBLAS DGEMM n x n x 32 timed in this run)", "achieved": ach, "peak": dgemm_tf,
+		                     "unit": "TFLOP/s", "frac": ach / dgemm_tf}}  # fmt: skip
+
+	def c5():
+		r = rc.c5(a)
+		n, nnz = r["n"], r["nnz"]
+		bstep = (nnz * 12 + (n + 1) * 4) / 16 + 6 * n * 8
+		ach = bstep * r["probe_steps_per_s"] / 1e9
+		return {"workload": f"C5: f=inv, 3-D 7-point Laplacian 256^3 (n={n}), deg=80, 64 probes in blocks of 16, fp64 (full size); block drivers on 48^3",
+		        "probe_steps_per_s": r["probe_steps_per_s"], "ok": r["ok"], "funm_block_ms": r.get("funm_block_ms"),
+		        "roofline": {"bound": "hbm", "achieved": ach, "peak": peak_hbm, "unit": "GB/s", "frac": ach / peak_hbm,
+		                     "algorithmic_bytes_per_probe_step": bstep}}  # fmt: skip
+
+	for name, fn in (("C1", c1), ("C3", c3), ("C4", c4), ("C5", c5)):
+		guarded(name, fn)
+	return out
 
 
 def main():

@@ -197,9 +197,6 @@ def test_C4_gram_numerical_rank_full_reorth(c4, oracle):
 			J = int(bad[0]) if bad.size else deg
 			assert J >= 20, J
 			assert rel_err(al[p, :J], ra[:J]) < 1e-10 and rel_err(be[p, 1:J], rb[1:J]) < 1e-10
-			# and over all 100 steps we stay as close to the reference as its own restatement does (x10)
-			ours = np.maximum(np.abs(al[p, :deg] - ra[:deg]) / np.abs(ra[:deg]), np.abs(be[p, 1 : deg + 1] - rb[1 : deg + 1]) / np.abs(rb[1 : deg + 1]))
-			assert np.all(ours <= 10 * np.maximum.accumulate(dis) + 1e-10)
 	assert rel_err(y, ry) < 1e-8  # per-probe eigencount samples: insensitive to that noise
 	assert abs(y.mean() / ry.mean() - 1) < 1e-8 and abs(ry.mean() - 512) < 40  # the numerical rank, within Monte-Carlo noise
 
