@@ -121,6 +121,34 @@ int slq_block_scatter_rows(const void* in_dev, const int32_t* idx_dev, int64_t n
  * primate.random.isotropic(pdf="rademacher") drawn column by column from that generator. */
 int slq_probes_rademacher(const uint64_t state_hi_lo[2], const uint64_t inc_hi_lo[2], uint64_t first_probe,
                           int k, int64_t n, int dtype, void* X_dev, slq_stream stream);
+/* ---- normal / sphere probes (src/primate/random.py:32-41 on NumPy's ziggurat, distributions.c random_standard_normal) --- */
+/* NumPy version whose ziggurat tables are compiled in (bit-exactness is pinned against that NumPy). */
+const char* slq_normals_numpy_version(void);
+/* Scratch for a scan of `nraw` raw draws (slq_normals_scan / slq_probes_normal). */
+size_t slq_normals_workspace_bytes(int64_t nraw);
+/* A normal variate consumes a data-dependent number of raw draws, so "where does probe i start" needs a scan.  Scans
+ * `nraw` raw draws from raw offset `raw_base` of the stream (a sample start) on the device: *total_dev = number of
+ * samples that start inside; if 0 <= target_ordinal < that, *raw_out_dev = raw position (relative to raw_base) where
+ * sample #target_ordinal starts.  Used to give every rank O(1)-communication random access to its probe range. */
+int slq_normals_scan(const uint64_t state_hi_lo[2], const uint64_t inc_hi_lo[2], uint64_t raw_base, int64_t nraw,
+                     int64_t target_ordinal, int64_t* total_dev, uint64_t* raw_out_dev, void* workspace_dev,
+                     size_t workspace_bytes, slq_stream stream);
+/* Standard-normal probe block, bit-exact with Generator.standard_normal drawn column by column: X[r*k + p] (float64)
+ * = sample #(p*n + r) of the stream starting at raw offset raw_base (a sample start).  nraw >= n*k raw positions are
+ * scanned (about 1.022 n k are needed); *end_raw_dev = raw draws the block consumed, or UINT64_MAX if nraw was too
+ * small (retry with more).  The ~2.6e-4 tail samples are also listed -- tail_ord[i] = (ordinal << 1) | negative,
+ * tail_raw[i] = raw draw U1 -- so that the caller can recompute  +-(r + (-log1p(-U1) / r))  with the host's libm (the
+ * one NumPy calls) and overwrite them: every other sample does not depend on libm's last bit. */
+int slq_probes_normal(const uint64_t state_hi_lo[2], const uint64_t inc_hi_lo[2], uint64_t raw_base, int64_t nraw, int k,
+                      int64_t n, double* X_dev, uint64_t* end_raw_dev, uint64_t* tail_count_dev, int64_t tail_cap,
+                      int64_t* tail_ord_dev, uint64_t* tail_raw_dev, void* workspace_dev, size_t workspace_bytes,
+                      slq_stream stream);
+/* In-place sphere scaling X[:, p] *= sqrt(n) / ||X[:, p]|| of a float64 block, the norms summed in NumPy's pairwise
+ * order (np.sum(W**2, axis=0): blocks of <= 128 with 8 accumulators, halved at multiples of 8).  leaf_start/leaf_len
+ * list the blocks, reduce_after[i] the number of pair-additions after block i; S_dev nleaves*k doubles, norm2_dev k. */
+int slq_probes_sphere_scale(double* X_dev, int64_t n, int k, const int64_t* leaf_start_dev, const int32_t* leaf_len_dev,
+                            const int32_t* reduce_after_dev, int64_t nleaves, double* S_dev, double* norm2_dev,
+                            slq_stream stream);
 /* Raw PCG64 outputs #offset.. (testing aid for the generator itself). */
 int slq_pcg64_raw(const uint64_t state_hi_lo[2], const uint64_t inc_hi_lo[2], uint64_t offset, int64_t count,
                   uint64_t* out_dev, slq_stream stream);

@@ -47,6 +47,13 @@ _SIGNATURES = {
 	"slq_block_gather_rows": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p, c_void_p]),
 	"slq_block_scatter_rows": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p, c_void_p]),
 	"slq_probes_rademacher": (c_int, [POINTER(c_uint64), POINTER(c_uint64), c_uint64, c_int, c_int64, c_int, c_void_p, c_void_p]),
+	"slq_normals_numpy_version": (c_char_p, []),
+	"slq_normals_workspace_bytes": (c_size_t, [c_int64]),
+	"slq_normals_scan": (c_int, [POINTER(c_uint64), POINTER(c_uint64), c_uint64, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_size_t,
+	                             c_void_p]),
+	"slq_probes_normal": (c_int, [POINTER(c_uint64), POINTER(c_uint64), c_uint64, c_int64, c_int, c_int64, c_void_p, c_void_p, c_void_p,
+	                              c_int64, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+	"slq_probes_sphere_scale": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p]),
 	"slq_pcg64_raw": (c_int, [POINTER(c_uint64), POINTER(c_uint64), c_uint64, c_int64, c_void_p, c_void_p]),
 	"slq_block_from_columns": (c_int, [c_void_p, c_int64, c_int, c_int, c_void_p, c_void_p]),
 	"slq_block_to_columns": (c_int, [c_void_p, c_int64, c_int, c_int, c_void_p, c_void_p]),

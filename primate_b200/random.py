@@ -4,9 +4,9 @@
 NumPy PCG64 stream, random.py:22-29,74-78).  The estimators do not call it on the hot path: they use
 `ProbeStream`, which produces the SAME probes directly in GPU memory -- Rademacher probes by jump-ahead into the
 PCG64 stream on the device (csrc/slq_probes.cu; probe i = stream elements [i*N, (i+1)*N), sign = top bit of the raw
-output), normal/sphere probes by the host generator plus one upload (NumPy's ziggurat consumes a data-dependent
-number of raw draws, so the stream position of a normal variate is inherently sequential).  Either way
-the user's Generator ends up advanced exactly as the reference would leave it.
+output), normal/sphere probes by NumPy's own ziggurat restated on the device (csrc/slq_normals.cu: the data-dependent
+number of raw draws per variate is resolved by a self-synchronising parallel scan).  Either way the
+user's Generator ends up advanced exactly as the reference would leave it.
 """
 import concurrent.futures
 import multiprocessing
@@ -74,8 +74,47 @@ def isotropic(
 	return _isotropic if size is None else _isotropic(size)
 
 
+ZIG_R = 3.6541528853610087963519472518  # NumPy's ziggurat_nor_r / ziggurat_nor_inv_r (ziggurat_constants.h)
+ZIG_INV_R = 0.27366123732975827203338247596
+_SEEK_CHUNK = 1 << 27  # raw draws scanned per seek launch
+_PLAN_CACHE: dict = {}
+
+
+def _pairwise_plan(n: int):
+	"""NumPy's pairwise summation of n contiguous doubles (numpy/_core/src/umath/loops_utils.h.src: pairwise_sum) as a
+	list of leaf blocks (start, length <= 128) plus, per leaf, the number of pair-additions to perform after it on a
+	stack machine -- what `np.sum(W**2, axis=0)` does per column of an F-ordered array (random.py:38)."""
+	if n in _PLAN_CACHE:
+		return _PLAN_CACHE[n]
+	starts, lens, red = [], [], []
+	stack = [(0, n, False)]  # (start, length, right-child-done marker)
+	while stack:
+		start, length, marker = stack.pop()
+		if marker:
+			red[-1] += 1
+			continue
+		if length <= 128:
+			starts.append(start)
+			lens.append(length)
+			red.append(0)
+			continue
+		n2 = length // 2
+		n2 -= n2 % 8
+		stack.append((0, 0, True))  # after both children: one addition
+		stack.append((start + n2, length - n2, False))
+		stack.append((start, n2, False))
+	plan = (np.asarray(starts, dtype=np.int64), np.asarray(lens, dtype=np.int32), np.asarray(red, dtype=np.int32))
+	_PLAN_CACHE[n] = plan
+	return plan
+
+
 class ProbeStream:
-	"""Device-resident view of the probe sequence `isotropic(pdf=..., seed=...)` would produce column by column."""
+	"""Device-resident view of the probe sequence `isotropic(pdf=..., seed=...)` would produce column by column.
+
+	Rademacher probes are a pure function of (seed, probe index): random access by LCG jump-ahead.  Normal / sphere
+	probes consume a data-dependent number of raw draws each (NumPy's ziggurat), so the stream position of probe i is
+	found by a device scan (libslq: slq_normals_scan) from the nearest known position; the positions of the block
+	boundaries met so far are remembered, so sequential use never scans twice."""
 
 	def __init__(self, n: int, pdf: str = "rademacher", seed: Union[int, np.random.Generator, None] = None, dtype=np.float64):
 		assert pdf in _ISO_DISTRIBUTIONS.keys(), f"Invalid distribution '{pdf}' supplied."
@@ -84,11 +123,108 @@ class ProbeStream:
 		self.dtype = np.dtype(dtype)
 		self.rng = np.random.default_rng(seed)
 		bg = self.rng.bit_generator
-		self.on_device = self.pdf == "rademacher" and isinstance(bg, np.random.PCG64)
+		self.on_device = isinstance(bg, np.random.PCG64)
 		if self.on_device:
 			st = bg.state["state"]
 			self._state, self._inc = int(st["state"]), int(st["inc"])
 		self.position = 0  # probes handed out so far
+		self._raw_at = {0: 0}  # normal / sphere: probe index -> raw draws consumed before it
+		self._plan_dev = None
+
+	# ---- normal / sphere on the device ------------------------------------------------------------------------------
+	def _scan_ws(self, nraw: int):
+		from . import _ffi, engine
+
+		torch = engine._torch()
+		need = _ffi.lib().slq_normals_workspace_bytes(int(nraw))
+		ws = getattr(self, "_ws", None)
+		if ws is None or ws.numel() < need:
+			ws = self._ws = torch.empty(need, dtype=torch.uint8, device="cuda")
+		return ws
+
+	def _raw_offset(self, probe: int) -> int:
+		"""Raw draws consumed by probes [0, probe) of the normal stream (exact)."""
+		from . import _ffi, engine
+
+		probe = int(probe)
+		if probe in self._raw_at:
+			return self._raw_at[probe]
+		torch = engine._torch()
+		L = _ffi.lib()
+		start = max(p for p in self._raw_at if p <= probe)
+		base, remaining = self._raw_at[start], (probe - start) * self.n
+		total = torch.zeros(1, dtype=torch.int64, device="cuda")
+		raw_out = torch.zeros(1, dtype=torch.int64, device="cuda")
+		st, inc = _ffi.u128_pair(self._state), _ffi.u128_pair(self._inc)
+		while remaining > 0:
+			nraw = int(min(_SEEK_CHUNK, remaining * 1.03 + 8192))
+			ws = self._scan_ws(nraw)
+			# first launch: how many samples start in the chunk; second: locate the wanted one (or the chunk's last)
+			_ffi.check(L.slq_normals_scan(st, inc, base, nraw, -1, total.data_ptr(), None, ws.data_ptr(), ws.numel(), engine._stream_ptr()))
+			have = int(total.item())
+			want = remaining if remaining < have else have - 1
+			_ffi.check(L.slq_normals_scan(st, inc, base, nraw, want, total.data_ptr(), raw_out.data_ptr(), ws.data_ptr(), ws.numel(),
+			                              engine._stream_ptr()))  # fmt: skip
+			base += int(raw_out.item())
+			remaining -= want
+		self._raw_at[probe] = base
+		return base
+
+	def _normal_block(self, k: int, first: int):
+		"""float64 device block (n, k) of standard normals for probes [first, first + k), bit-exact with NumPy."""
+		import math
+
+		from . import _ffi, engine
+
+		torch = engine._torch()
+		L = _ffi.lib()
+		n = self.n
+		base = self._raw_offset(first)
+		X = torch.empty((n, k), dtype=torch.float64, device="cuda")
+		end_raw = torch.zeros(1, dtype=torch.int64, device="cuda")
+		tail_count = torch.zeros(1, dtype=torch.int64, device="cuda")
+		cap = int(n * k * 1e-3) + 4096  # expected tail samples: 2.6e-4 n k
+		tail_ord = torch.empty(cap, dtype=torch.int64, device="cuda")
+		tail_raw = torch.empty(cap, dtype=torch.int64, device="cuda")
+		st, inc = _ffi.u128_pair(self._state), _ffi.u128_pair(self._inc)
+		nraw = int(n * k * 1.03) + 8192
+		while True:
+			ws = self._scan_ws(nraw)
+			_ffi.check(L.slq_probes_normal(st, inc, base, nraw, int(k), n, X.data_ptr(), end_raw.data_ptr(), tail_count.data_ptr(), cap,
+			                               tail_ord.data_ptr(), tail_raw.data_ptr(), ws.data_ptr(), ws.numel(), engine._stream_ptr()))  # fmt: skip
+			used = int(end_raw.item())
+			if used >= 0:  # UINT64_MAX (read as -1): the scan was too short for n*k samples
+				break
+			nraw = int(nraw * 1.05) + 65536
+		self._raw_at[first + k] = base + used
+		# tail samples with the host's libm, exactly as NumPy computes them (distributions.c: random_standard_normal)
+		nt = int(tail_count.item())
+		assert nt <= cap, "tail list overflow"
+		if nt:
+			ords = tail_ord[:nt].cpu().numpy()
+			raws = tail_raw[:nt].cpu().numpy().view(np.uint64)
+			vals = np.empty(nt)
+			for i in range(nt):
+				xx = -ZIG_INV_R * math.log1p(-(float(int(raws[i]) >> 11) * (1.0 / 9007199254740992.0)))
+				vals[i] = -(ZIG_R + xx) if (int(ords[i]) & 1) else ZIG_R + xx
+			o = ords >> 1
+			flat = torch.from_numpy((o % n) * k + o // n).cuda()
+			X.view(-1)[flat] = torch.from_numpy(vals).cuda()
+		return X
+
+	def _sphere_scale(self, X) -> None:
+		from . import _ffi, engine
+
+		torch = engine._torch()
+		n, k = int(X.shape[0]), int(X.shape[1])
+		if self._plan_dev is None:
+			starts, lens, red = _pairwise_plan(n)
+			self._plan_dev = (torch.from_numpy(starts).cuda(), torch.from_numpy(lens).cuda(), torch.from_numpy(red).cuda())
+		starts, lens, red = self._plan_dev
+		S = torch.empty(starts.numel() * k, dtype=torch.float64, device="cuda")
+		norm2 = torch.empty(k, dtype=torch.float64, device="cuda")
+		_ffi.check(_ffi.lib().slq_probes_sphere_scale(X.data_ptr(), n, k, starts.data_ptr(), lens.data_ptr(), red.data_ptr(),
+		                                              int(starts.numel()), S.data_ptr(), norm2.data_ptr(), engine._stream_ptr()))  # fmt: skip
 
 	def block(self, k: int, first: Optional[int] = None):
 		"""Device probe block (n, k) for probes [first, first+k) (default: the next k); rows = vector entries."""
@@ -96,7 +232,14 @@ class ProbeStream:
 
 		if self.on_device:
 			first = self.position if first is None else int(first)
-			X = engine.rademacher_block(self._state, self._inc, first, k, self.n, self.dtype)
+			if self.pdf == "rademacher":
+				X = engine.rademacher_block(self._state, self._inc, first, k, self.n, self.dtype)
+			else:
+				X = self._normal_block(int(k), first)
+				if self.pdf == "sphere":
+					self._sphere_scale(X)
+				if self.dtype != np.float64:
+					X = X.to(engine._tdtype(self.dtype))  # the reference casts after generating float64 (trace.py:108,115)
 			self.position = max(self.position, first + k)
 			return X
 		if first is not None and first > self.position:
@@ -117,9 +260,13 @@ class ProbeStream:
 			self.position += int(count)
 
 	def finish(self, consumed: int) -> None:
-		"""Leaves the user's Generator where the reference would: `consumed` probes of n raw draws each."""
-		if self.on_device:
-			self.rng.bit_generator.advance(int(consumed) * self.n)
+		"""Leaves the user's Generator where the reference would: advanced by exactly the raw draws the first `consumed`
+		probes use (n each for Rademacher; the scanned, data-dependent count for normal / sphere probes).  A generator
+		that is not PCG64 was drawn from directly on the host and is already where the probes handed out left it."""
+		if not self.on_device:
+			return
+		raws = int(consumed) * self.n if self.pdf == "rademacher" else self._raw_offset(int(consumed))
+		self.rng.bit_generator.advance(raws)
 
 
 class Isotropic:
