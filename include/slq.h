@@ -234,6 +234,25 @@ int slq_lanczos_replay(slq_op* op, const void* X_dev, int k, int deg, const void
                        const int32_t* steps_dev, const double* xnorm2_dev, const double* coeffs_dev, void* Y_dev,
                        void* workspace_dev, size_t workspace_bytes, slq_stream stream);
 
+/* ---- tall-skinny panel algebra for the block drivers (replaces NumPy/LAPACK on host panels: np.linalg.qr, Q.T @ G,
+ * Q @ S, einsum row/column dots -- src/primate/trace.py:158-175,201-227, diagonal.py:115-137) -------------------------------
+ * Panels are n x m row-major device arrays with a row stride ld (elements); m x m results are fp64.  Deterministic. */
+/* G[a x b] (doubles, row-major) = X[row0:row1, :a]^T Y[row0:row1, :b]  -- Gram matrices and projections; a row range
+ * so that ranks can each reduce a slice of replicated panels and all-reduce a*b doubles. */
+size_t slq_panel_gram_workspace_bytes(int a, int b);
+int slq_panel_gram(const void* X_dev, int a, int64_t ldx, const void* Y_dev, int b, int64_t ldy, int64_t row0, int64_t row1,
+                   int dtype, double* G_dev, void* workspace_dev, size_t workspace_bytes, slq_stream stream);
+/* Y[n x b] = alpha X[n x a] S[a x b] + beta Y  (S: doubles, row-major; X != Y): Q = Y R^-1, G -= Q (Q^T G), Q S, ... */
+int slq_panel_matmul(const void* X_dev, int a, int64_t ldx, const double* S_dev, int b, double alpha, double beta, void* Y_dev,
+                     int64_t ldy, int64_t n, int dtype, slq_stream stream);
+/* out[r] = sum_j X[r][j] Y[r][j]  (n doubles): the diagonal of X Y^T. */
+int slq_panel_rowdot(const void* X_dev, int64_t ldx, const void* Y_dev, int64_t ldy, int m, int64_t n, int dtype, double* out_dev,
+                     slq_stream stream);
+/* out[j] = sum over rows [row0, row1) of X[r][j] Y[r][j]  (m doubles): the diagonal of X^T Y. */
+size_t slq_panel_coldot_workspace_bytes(int m);
+int slq_panel_coldot(const void* X_dev, int64_t ldx, const void* Y_dev, int64_t ldy, int m, int64_t row0, int64_t row1, int dtype,
+                     double* out_dev, void* workspace_dev, size_t workspace_bytes, slq_stream stream);
+
 #if defined(__GNUC__)
 #pragma GCC visibility pop
 #endif

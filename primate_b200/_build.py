@@ -22,7 +22,7 @@ INCLUDE = os.path.join(ROOT, "include")
 OBJ_DIR = os.path.join(PKG, "csrc", "build")
 LIB = os.path.join(PKG, "libslq.so")
 SOURCES = [
-	"slq_api.cu", "slq_lanczos.cu", "slq_lanczos_f64.cu", "slq_lanczos_f32.cu", "slq_probes.cu", "slq_normals.cu", "slq_quadrature.cu",
+	"slq_api.cu", "slq_lanczos.cu", "slq_lanczos_f64.cu", "slq_lanczos_f32.cu", "slq_probes.cu", "slq_normals.cu", "slq_panels.cu", "slq_quadrature.cu",
 	"slq_reorder.cu",
 ]  # fmt: skip
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")

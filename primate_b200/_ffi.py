@@ -73,6 +73,14 @@ _SIGNATURES = {
 	"slq_replay_workspace_bytes": (c_size_t, [c_int64, c_int, c_int, c_int]),
 	"slq_lanczos_replay": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
 	                               c_size_t, c_void_p]),
+	"slq_panel_gram_workspace_bytes": (c_size_t, [c_int, c_int]),
+	"slq_panel_gram": (c_int, [c_void_p, c_int, c_int64, c_void_p, c_int, c_int64, c_int64, c_int64, c_int, c_void_p, c_void_p, c_size_t,
+	                           c_void_p]),
+	"slq_panel_matmul": (c_int, [c_void_p, c_int, c_int64, c_void_p, c_int, c_double, c_double, c_void_p, c_int64, c_int64, c_int, c_void_p]),
+	"slq_panel_rowdot": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int, c_int64, c_int, c_void_p, c_void_p]),
+	"slq_panel_coldot_workspace_bytes": (c_size_t, [c_int]),
+	"slq_panel_coldot": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int, c_int64, c_int64, c_int, c_void_p, c_void_p, c_size_t,
+	                             c_void_p]),
 	"slq_basis_combine": (c_int, [c_void_p, c_int64, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
 }  # fmt: skip
 

@@ -7,7 +7,7 @@ import scipy as sp
 
 from .estimators import ConvergenceCriterion, EstimatorResult, MeanEstimator, convergence_criterion
 from .operators import MatrixFunction, is_valid_operator
-from .random import ProbeStream, isotropic
+from .random import isotropic
 
 
 def diag(
@@ -50,73 +50,34 @@ def diag(
 
 def xdiag(A: np.ndarray, m: Optional[int] = None, pdf: str = "sphere", seed: Union[int, np.random.Generator, None] = None):
 	"""XDiag (Epperly et al.) estimate of the diagonal of `A` from `m / 2` block products with `A` and `A.T`
-	(diagonal.py:99-138)."""
+	(diagonal.py:99-138).  On a `MatrixFunction` (symmetric: A.T = A) the n x m panels N, A N, Q, A Q stay on the GPU and
+	are reduced by libslq's panel kernels (primate_b200.panels.DevicePanels); only m x m matrices reach the host."""
+	from . import panels
+	from .trace import _panel_backend
+
 	m = 2 * A.shape[0] if m is None else min(m + (m % 2), 2 * A.shape[0])
 	n, m = A.shape[0], m // 2
-	if isinstance(A, MatrixFunction) and isinstance(pdf, str):
-		return _xdiag_device(A, n, m, pdf, np.random.default_rng(seed=seed))
-
-	def dprod(X, Y):  # diag(X Y^T) of two (n, m) panels, as a column
-		return np.einsum("ij,ij->i", X, Y)[:, np.newaxis]
-
 	rng = np.random.default_rng(seed=seed)
-	draw = isotropic(pdf=pdf, seed=rng)
+	P, finish = _panel_backend(A, pdf, rng, A.dtype if hasattr(A, "dtype") and np.dtype(A.dtype).kind == "f" else np.float64)
 
-	Nw = draw(size=(n, m))
-	Y = A @ Nw
-	Q, R = np.linalg.qr(Y, mode="reduced")
-	dNY = dprod(Nw, Y)
+	Nw = P.probes(0, m)
+	finish(m)
+	Y = P.product(Nw)
+	Q, R = P.qr(Y)
+	dNY = P.rowdot(Nw, Y)
 	del Y
+	Z = P.product(Q) if P.on_device else A.T @ Q
 
-	Z = A.T @ Q
-	T = Z.T @ Nw
-	R_inv = np.linalg.inv(R)
+	## m x m quantities (host)
+	T = P.gram(Z, Nw)
+	R_inv = panels.upper_inverse(R)
 	S = R_inv.T / np.linalg.norm(R_inv, axis=1)
-	QS = Q @ S
+	dST = np.einsum("ij,ij->j", S, T)
 
-	dQZ = dprod(Q, Z)
-	dQSSZ = dprod(QS, Z @ S)
-	dNTQ = dprod(Nw, Q @ T)
-	dST = np.einsum("ij,ij->j", S, T)  # diag(S^T T)
-	dNQSST = dprod(Nw, QS * dST[np.newaxis, :])
-
+	## diagonals of the n x n products, one row-dot of two panels each
+	dQZ = P.rowdot(Q, Z)
+	dQSSZ = P.rowdot(P.matmul(Q, S), P.matmul(Z, S))
+	dNTQ = P.rowdot(Nw, P.matmul(Q, T))
+	dNQSST = P.rowdot(Nw, P.matmul(Q, S * dST[np.newaxis, :]))
 	d = dQZ + (-dQSSZ + dNY - dNTQ + dNQSST) / m
-	return d.ravel()
-
-
-def _xdiag_device(A: MatrixFunction, n: int, m: int, pdf: str, rng: np.random.Generator) -> np.ndarray:
-	"""XDiag with every n x m panel resident on the GPU: the same formulas as above on the same probes (device generator
-	for Rademacher probes, host generator + one upload otherwise), block products from the Lanczos engine (columns split
-	over the ranks when the MatrixFunction has a `comm`), thin QR / small inverses from torch on the same device."""
-	import torch
-
-	from . import engine
-
-	stream = ProbeStream(n, pdf, seed=rng, dtype=A.dtype)
-	cols, off = [], 0
-	for k in engine.block_sizes(m, 64):
-		cols.append(stream.block(k, off))
-		off += k
-	Nw = torch.cat(cols, dim=1) if len(cols) > 1 else cols[0]
-	stream.finish(m)
-	del cols
-
-	Y = A.matmat_device(Nw)
-	Q, R = torch.linalg.qr(Y, mode="reduced")
-	dNY = (Nw * Y).sum(dim=1)
-	del Y
-
-	Z = A.matmat_device(Q)  # A.T @ Q: a matrix function of a symmetric operator is its own transpose
-	T = Z.T @ Nw
-	R_inv = torch.linalg.inv(R)
-	S = R_inv.T / torch.linalg.norm(R_inv, dim=1)
-	QS = Q @ S
-
-	dQZ = (Q * Z).sum(dim=1)
-	dQSSZ = (QS * (Z @ S)).sum(dim=1)
-	dNTQ = (Nw * (Q @ T)).sum(dim=1)
-	dST = (S * T).sum(dim=0)
-	dNQSST = (Nw * (QS * dST[None, :])).sum(dim=1)
-
-	d = dQZ + (-dQSSZ + dNY - dNTQ + dNQSST) / m
-	return d.double().cpu().numpy().ravel()
+	return np.ravel(P.to_host(d))

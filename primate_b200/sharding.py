@@ -61,6 +61,11 @@ class Comm:
 		self._dist.all_gather_into_tensor(out, t, group=self.group)
 		return out
 
+	def all_reduce_sum(self, t):
+		"""In-place sum of a tensor on the backend's device over the ranks (every rank gets the same bits)."""
+		self._dist.all_reduce(t, op=self._dist.ReduceOp.SUM, group=self.group)
+		return t
+
 	def barrier(self):
 		self._dist.barrier(group=self.group)
 

@@ -23,7 +23,8 @@ from .estimators import (
 	MeanEstimator,
 	convergence_criterion,
 )
-from .linalg import update_trinv
+from . import panels
+from .linalg import append_trinv
 from .operators import MatrixFunction, is_valid_operator
 from .random import ProbeStream, isotropic
 
@@ -230,11 +231,16 @@ def hutch(
 	return estimator.estimate
 
 
-def _quad_columns(A, Q: np.ndarray) -> np.ndarray:
-	"""q^T A q for every column of Q (one blocked device call for a MatrixFunction)."""
-	if hasattr(A, "quad"):
-		return np.ravel(A.quad(Q))
-	return np.einsum("ij,ij->j", Q, A @ Q)
+def _panel_backend(A, pdf, rng: np.random.Generator, f_dtype):
+	"""(panel backend, finish) for a block driver: device panels + device probes for a `MatrixFunction` with a named
+	pdf on a PCG64 generator, NumPy panels otherwise.  `finish(consumed)` leaves the user's Generator where the
+	reference would (host samplers draw from it directly, so there it is a no-op)."""
+	if isinstance(A, MatrixFunction) and isinstance(pdf, str):
+		stream = ProbeStream(A.shape[0], pdf, seed=rng, dtype=f_dtype)
+		if stream.on_device:
+			return panels.DevicePanels(A, stream), stream.finish
+	draw = isotropic(pdf=pdf, seed=rng) if isinstance(pdf, str) else pdf
+	return panels.HostPanels(A, draw, f_dtype), (lambda consumed: None)
 
 
 def hutchpp(
@@ -249,8 +255,8 @@ def hutchpp(
 	"""Hutch++ estimator (trace.py:119-182): exact trace on a sketched range + Hutchinson on the deflated remainder.
 
 	`m` probes go to each of the two phases (default n // 3, bumped by `m % 3` as in the reference); `batch` is
-	unused.  All products with `A` are block products (`A @ block`), i.e. blocked device Lanczos for a MatrixFunction.
-	"""
+	unused.  mode "full" evaluates the sketched part as diag(Q^T A Q), any other mode through `A.quad` when the operator
+	has one.  On a `MatrixFunction` every n x m panel stays on the GPU (primate_b200.panels.DevicePanels)."""
 	f_dtype = is_valid_operator(A)
 	N: int = A.shape[0]
 	rng = np.random.default_rng(seed)
@@ -259,98 +265,39 @@ def hutchpp(
 
 	nb = (N // 3) if m is None else m
 	nb += nb % 3
-	if isinstance(A, MatrixFunction) and isinstance(pdf, str) and mode in ("reduced", "full"):
-		stream = ProbeStream(N, pdf, seed=rng, dtype=f_dtype)
-		if stream.on_device:
-			return _hutchpp_device(A, nb, mode, stream, full)
-	draw = isotropic(pdf=pdf, seed=rng)
+	P, finish = _panel_backend(A, pdf, rng, f_dtype)
 
-	## range sketch
-	WB = draw(size=(N, nb)).astype(f_dtype)
-	Q = np.linalg.qr(A @ WB, mode="reduced")[0]
-	rng_ests = np.einsum("ij,ij->j", A @ Q, Q) if mode == "full" else _quad_columns(A, Q)
-	tr_rng = np.sum(rng_ests)
+	## range sketch: Q = orth(A W)
+	Q = P.qr(P.product(P.probes(0, nb)))[0]
+	rng_ests = P.coldot(P.product(Q), Q) if mode == "full" else P.quad(Q)
 
-	## Hutchinson on the complement of range(Q)
-	G = draw(size=(N, nb)).astype(f_dtype)
-	G -= Q @ (Q.T @ G)
-	defl_ests = np.einsum("ij,ij->j", A @ G, G)
-	tr_defl = np.sum(defl_ests) / nb
+	## Hutchinson on the complement of range(Q): G <- (I - Q Q^T) G
+	G = P.probes(nb, nb)
+	P.axpy_matmul(G, Q, P.gram(Q, G))
+	defl_ests = P.coldot(P.product(G), G)
+	finish(2 * nb)
 
+	estimate = float(np.sum(rng_ests) + np.sum(defl_ests) / nb)
 	if not full:
-		return tr_rng + tr_defl
+		return estimate
 	result = EstimatorResult()
-	result.estimate = tr_rng + tr_defl
+	result.estimate = estimate
 	result.nit = 2 * nb
-	result.samples = np.concatenate([np.ravel(rng_ests), defl_ests])
+	result.samples = np.concatenate([np.ravel(rng_ests), np.ravel(defl_ests)])
 	return result.estimate, result
 
 
-def _hutchpp_device(A: MatrixFunction, nb: int, mode: str, stream: ProbeStream, full: bool):
-	"""Hutch++ with every panel resident on the GPU (same estimator, same probes as the host path above): the probes
-	come from the device generator (the columns `isotropic` would draw, in order), the block products and quadratic
-	forms from the Lanczos engine (columns split over the ranks when the MatrixFunction has a `comm`), and the thin QR /
-	projection -- library algebra in the reference too (np.linalg.qr) -- from torch on the same device."""
-	import torch
-
-	from . import engine
-
-	def draw(first: int, count: int):
-		cols, off = [], 0
-		for k in engine.block_sizes(count, 64):
-			cols.append(stream.block(k, first + off))
-			off += k
-		return torch.cat(cols, dim=1) if len(cols) > 1 else cols[0]
-
-	## range sketch
-	WB = draw(0, nb)
-	Q = torch.linalg.qr(A.matmat_device(WB), mode="reduced")[0]
-	del WB
-	rng_ests = (A.matmat_device(Q) * Q).sum(dim=0) if mode == "full" else A.quad_device(Q)
-	tr_rng = float(rng_ests.sum().item())
-
-	## Hutchinson on the complement of range(Q)
-	G = draw(nb, nb)
-	G -= Q @ (Q.T @ G)
-	defl_ests = (A.matmat_device(G) * G).sum(dim=0)
-	tr_defl = float(defl_ests.sum().item()) / nb
-	stream.finish(2 * nb)
-
-	if not full:
-		return tr_rng + tr_defl
-	result = EstimatorResult()
-	result.estimate = tr_rng + tr_defl
-	result.nit = 2 * nb
-	result.samples = np.concatenate([rng_ests.double().cpu().numpy().ravel(), defl_ests.double().cpu().numpy().ravel()])
-	return result.estimate, result
-
-
-def _xtrace(W: np.ndarray, Z: np.ndarray, Q: np.ndarray, R: np.ndarray, R_inv: np.ndarray, pdf: str):
-	"""Leave-one-out XTrace samples (trace.py:185-227) from the probes W, Q/R of qr(A W), Z = A Q and R^{-1}."""
-
-	def dprod(X, Y):  # diag(X^T Y) as a column
-		return np.einsum("ij,ij->j", X, Y)[:, np.newaxis]
-
-	n, m = W.shape
-	QtW = Q.T @ W
-	S = R_inv.T / np.linalg.norm(R_inv, axis=1)  # unit-norm columns spanning the leave-one-out directions
-
-	if not pdf == "sphere":
-		scale = np.ones((m, 1))
-	else:
-		cn = lambda X: np.linalg.norm(X, axis=0)  # noqa: E731
-		scale = (n - m + 1) / (n - (cn(QtW)[:, np.newaxis]) ** 2 + (dprod(S, QtW) * cn(S)[:, np.newaxis]) ** 2)
-
-	H = Q.T @ Z
-	HW = H @ QtW
-	T = Z.T @ W
-	dSW, dSHS = dprod(S, QtW), dprod(S, H @ S)
-	dTW, dWHW = dprod(T, QtW), dprod(QtW, HW)
-	dSRmHW, dTmHRS = dprod(S, R - HW), dprod(T - H.T @ QtW, S)
-
-	ests = np.trace(H) * np.ones((m, 1)) - dSHS
-	ests += (-dTW + dWHW + dSW * dSRmHW + abs(dSW) ** 2 * dSHS + dTmHRS * dSW) * scale
-	return ests
+def _xtrace_samples(Wq: np.ndarray, H: np.ndarray, T: np.ndarray, R: np.ndarray, R_inv: np.ndarray) -> np.ndarray:
+	"""The m leave-one-out XTrace samples (trace.py:185-227) from m x m matrices only: Wq = Q^T W, H = Q^T A Q,
+	T = (A Q)^T W and the QR factor R of A W with its inverse.  The reference hands `_xtrace` its sampler, not the pdf's
+	name, so the "sphere" rescaling branch (trace.py:209-214) never runs: scale = 1."""
+	cd = lambda X, Y: np.einsum("ij,ij->j", X, Y)  # noqa: E731  (diag(X^T Y))
+	S = R_inv.T / np.linalg.norm(R_inv, axis=1)  # unit columns: the direction each probe adds to the sketch
+	sw = cd(S, Wq)
+	shs = cd(S, H @ S)
+	HW = H @ Wq
+	resid = -cd(T, Wq) + cd(Wq, HW) + sw * cd(S, R - HW) + np.abs(sw) ** 2 * shs + cd(T - H.T @ Wq, S) * sw
+	return np.trace(H) - shs + resid
 
 
 def xtrace(
@@ -364,10 +311,12 @@ def xtrace(
 	**kwargs,
 ) -> Union[float, tuple]:
 	"""Epperly's exchangeable XTrace estimator (trace.py:233-315): grows a sketch batch by batch and averages the
-	leave-one-out estimates.  Signature and quirks are the reference's (a `CountCriterion(n)` is always in force and a
-	user `converge` is OR-ed onto it; the probes' `pdf` reaches `_xtrace` as a sampler, so no sphere rescaling)."""
-	from scipy.linalg import qr_insert
+	leave-one-out estimates.  Signature and quirks are the reference's: a `CountCriterion(n)` is always in force and a
+	user `converge` is OR-ed onto that same object (trace.py:271-276), so the loop runs until the sketch has n columns.
 
+	The sketch is appended to block-wise (two Gram-Schmidt sweeps against Q + a thin QR of the remainder: the batch form
+	of the reference's `qr_insert` per column), and the samples are formed from m x m matrices; on a `MatrixFunction`
+	the n x m panels W, Q, A Q live on the GPU."""
 	assert batch >= 1, "Batch size must be positive."
 	n = A.shape[0]
 	callback = (lambda result: ...) if not callable(callback) else callback
@@ -381,28 +330,28 @@ def xtrace(
 		converge |= convergence_criterion(converge, **kwargs)
 	assert isinstance(converge, ConvergenceCriterion)
 
-	W = np.zeros(shape=(n, 0), order="F")
-	Y = np.zeros(shape=(n, 0))
-	Z = np.zeros(shape=(n, 0), order="F")
-	Q, R = np.linalg.qr(Y, mode="reduced")
-	R_inv = np.zeros(shape=(0, 0))
-
 	result = EstimatorResult()
 	rng = np.random.default_rng(seed)
-	pdf = isotropic(pdf=pdf, seed=rng) if isinstance(pdf, str) else pdf
+	f_dtype = A.dtype if hasattr(A, "dtype") else np.float64
+	P, finish = _panel_backend(A, pdf, rng, np.dtype(f_dtype) if np.dtype(f_dtype).kind == "f" else np.float64)
+	W, Q, Z = P.empty(n), P.empty(n), P.empty(n)  # probes, orth(A W), A Q: n columns at most
+	R, R_inv, m = np.zeros((0, 0)), np.zeros((0, 0)), 0
 	while not converge(estimator):
-		ns = min(A.shape[1] - W.shape[1], int(batch))
-		Nw = pdf(size=(n, ns))
-		Y = A @ Nw
-		for j in range(ns):
-			Q, R = qr_insert(Q, R, u=Y[:, j], k=Q.shape[1], which="col")
-			R_inv = update_trinv(R_inv, R[:, -1])
-		W = np.c_[W, Nw]
-		Z = np.c_[Z, A @ Q[:, -ns:]]
-		t_samples = _xtrace(W, Z, Q, R, R_inv, pdf)
-		estimator = MeanEstimator(record=record)
-		estimator.update(t_samples.ravel())
+		ns = min(A.shape[1] - m, int(batch))
+		Nw = P.probes(m, ns)
+		Qn, C, Rn = panels.block_orthogonalize(P, P.cols(Q, 0, m) if m else None, P.product(Nw))
+		R_inv = append_trinv(R_inv, C if C is not None else np.zeros((0, ns)), panels.upper_inverse(Rn))
+		R = np.block([[R, C if C is not None else np.zeros((0, ns))], [np.zeros((ns, m)), Rn]])
+		P.assign(W, m, Nw)
+		P.assign(Q, m, Qn)
+		P.assign(Z, m, P.product(Qn))
+		m += ns
+		Wm, Qm, Zm = P.cols(W, 0, m), P.cols(Q, 0, m), P.cols(Z, 0, m)
+		t_samples = _xtrace_samples(P.gram(Qm, Wm), P.gram(Qm, Zm), P.gram(Zm, Wm), R, R_inv)
+		estimator = MeanEstimator(record=record)  # XTrace re-derives all m samples from the grown sketch
+		estimator.update(np.ravel(t_samples))
 		callback(result)
+	finish(m)
 
 	result.estimator = estimator
 	result.estimate = estimator.estimate

@@ -221,3 +221,28 @@ def test_hutchpp_xtrace_xdiag_diag_host_algebra_match_reference_golden(golden):
 	assert np.allclose(xdiag(A, m=20, seed=6), golden["xdiag_A_m20_seed6"], rtol=1e-9, atol=1e-11)
 	assert abs(xtrace(A, batch=10, seed=8) - golden["xtrace_A_b10_seed8"].item()) < 1e-8
 	assert np.allclose(diag(A, converge="count", count=50, seed=10), golden["diag_A_seed10"], rtol=1e-10, atol=1e-12)
+
+
+def test_no_library_linear_algebra_on_device_panels():
+	"""The device-panel drivers own their algebra: no torch.linalg / torch matmul on n x m panels (CholeskyQR2 and the
+	panel kernels of libslq instead); NumPy's dense solvers only ever see m x m matrices."""
+	import re
+
+	for fn in ("trace.py", "diagonal.py", "panels.py", "operators.py", "engine.py", "random.py"):
+		src = open(os.path.join(ROOT, "primate_b200", fn)).read()
+		assert "torch.linalg" not in src and "linalg.qr(" not in src.replace("np.linalg.qr(", ""), fn
+		assert not re.search(r"\btorch\.(matmul|mm|bmm)\b", src), fn
+
+
+def test_update_trinv_and_block_append():
+	"""src/primate/linalg.py:5-24 (tests/test_linalg.py:5-27): appending columns to an upper-triangular inverse."""
+	from primate_b200.linalg import append_trinv, update_trinv
+
+	rng = np.random.default_rng(0)
+	R = np.triu(rng.standard_normal((9, 9))) + 4 * np.eye(9)
+	Rinv = np.zeros((0, 0))
+	for j in range(9):
+		Rinv = update_trinv(Rinv, R[: j + 1, j])
+		assert np.allclose(Rinv, np.linalg.inv(R[: j + 1, : j + 1]), atol=1e-10)
+	blk = append_trinv(np.linalg.inv(R[:5, :5]), R[:5, 5:], np.linalg.inv(R[5:, 5:]))
+	assert np.allclose(blk, np.linalg.inv(R), atol=1e-10)
