@@ -132,6 +132,144 @@ __global__ void __launch_bounds__(DenseTiling<T, K, RPT>::NTD, 2)
   }
 }
 
+// ---- fp64 tensor-core variant (DMMA) -----------------------------------------------------------------------------------
+// Same producer/consumer ring, but the consumers issue mma.sync.m8n8k4.f64 (SASS DMMA) instead of scalar FMAs: the only
+// GEMM-shaped fp64 work on the path (north_star: "the only place fp64 DMMA tensor-core tiles are considered").
+// Each consumer warp owns 16 rows x K columns of Y: per k4 step 2 A fragments (As[kk][m], transposed tile = the
+// layout DMMA's row-major A fragment wants) + K/8 B fragments (the X slab) feed 2 K/8 DMMAs.  Shared-memory rows are
+// padded by 4 doubles: a 64-bit warp load is served one half-warp (lanes 0-15: g = 0..3, t = 0..3) at a time, and
+// with a row stride = 4 (mod 16) doubles the sixteen 8-byte words of a half-warp, t * stride + g, fall into sixteen
+// different bank pairs (2 wavefronts per warp load: the minimum; a pad of 8 measured 2x that, ncu r02g).  The fragment-to-lane maps are PTX's for m8n8k4 f64:
+//   A (8x4, row): lane l holds A[l / 4][l % 4];  B (4x8, col): lane l holds B[l % 4][l / 4];
+//   C (8x8): lane l holds C[l / 4][2 (l % 4)], C[l / 4][2 (l % 4) + 1].
+template <int K, int RPT>
+struct DmmaTiling {
+  static constexpr int TR = 16 * RPT;   // rows of Y per CTA: one 16-row slab per consumer warp
+  static constexpr int KC = 16;         // columns of A (rows of X) per stage
+  static constexpr int TRP = TR + 4;    // padded shared-memory row strides (doubles): = 4 (mod 16)
+  static constexpr int KP = K + 4;
+  static constexpr int CTAS = RPT > 8 ? 1 : 2;  // resident CTAs per SM the tiling is sized for
+  static constexpr size_t A_BYTES = (size_t)KC * TRP * sizeof(double);
+  static constexpr size_t X_BYTES = (size_t)KC * KP * sizeof(double);
+  static constexpr size_t STAGE_BYTES = A_BYTES + X_BYTES;
+  static constexpr int STAGES_FIT = (int)(((CTAS == 1 ? 216 : 110) * 1024) / STAGE_BYTES);
+  static constexpr int STAGES = STAGES_FIT > 8 ? 8 : (STAGES_FIT < 3 ? 3 : STAGES_FIT);
+  static constexpr int NCONS = 32 * RPT;
+  static constexpr int NTD = NCONS + 32;
+  static constexpr int NB = K / 8;      // 8-column blocks of Y
+  static_assert(TRP % 16 == 4 && (KP % 16 == 4 || KP % 16 == 12), "row strides must spread the four k-rows over the bank pairs");
+  static constexpr size_t SMEM_BYTES = STAGE_BYTES * STAGES;
+};
+
+__device__ __forceinline__ void dmma_884(double (&c)[2], double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c[0]), "+d"(c[1]) : "d"(a), "d"(b));
+}
+
+template <int K, int RPT>
+__global__ void __launch_bounds__(DmmaTiling<K, RPT>::NTD, DmmaTiling<K, RPT>::CTAS)
+    k_dense_dmma(int n, const double* __restrict__ A, int64_t ld, const double* __restrict__ X, double* __restrict__ Y) {
+  using D = DmmaTiling<K, RPT>;
+  constexpr int TR = D::TR, KC = D::KC, STAGES = D::STAGES, NB = D::NB, TRP = D::TRP, KP = D::KP;
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  __shared__ uint64_t bar_full[STAGES], bar_empty[STAGES];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int row0 = blockIdx.x * TR;
+  const int rows = min(TR, n - row0);  // n is a multiple of 16: whole 16-row warp slabs, whole 16-byte units
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&bar_full[s], 1);
+      mbar_init(&bar_empty[s], D::NCONS / 32);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  const int nchunks = n / KC;
+  if (warp == RPT) {  // ---- producer warp: KC slices of A (one per column, contiguous by symmetry) + KC rows of X
+    const uint32_t a_line = (uint32_t)(rows * sizeof(double));
+    constexpr uint32_t x_line = (uint32_t)(K * sizeof(double));
+    for (int c = 0; c < nchunks; ++c) {
+      const int s = c % STAGES;
+      if (c >= STAGES) mbar_wait(&bar_empty[s], (uint32_t)(((c / STAGES) - 1) & 1));
+      unsigned char* S = smem_raw + (size_t)s * D::STAGE_BYTES;
+      if (lane == 0) mbar_arrive_expect_tx(&bar_full[s], (uint32_t)(KC * a_line + KC * x_line));
+      __syncwarp();
+      if (lane < KC)
+        bulk_g2s(S + (size_t)lane * TRP * sizeof(double), A + (size_t)(c * KC + lane) * ld + row0, a_line, &bar_full[s]);
+      else
+        bulk_g2s(S + D::A_BYTES + (size_t)(lane - KC) * KP * sizeof(double), X + (size_t)(c * KC + lane - KC) * K, x_line, &bar_full[s]);
+    }
+    return;
+  }
+  // ---- consumer warps: rows [warp*16, warp*16 + 16) of the tile
+  const int g = lane >> 2, t = lane & 3;
+  const bool active = warp * 16 < rows;  // the last tile may hold fewer slabs (their smem rows are stale: never stored)
+  double acc[2][NB][2];
+#pragma unroll
+  for (int mb = 0; mb < 2; ++mb)
+#pragma unroll
+    for (int nb = 0; nb < NB; ++nb) acc[mb][nb][0] = acc[mb][nb][1] = 0.0;
+  for (int c = 0; c < nchunks; ++c) {
+    const int s = c % STAGES;
+    mbar_wait(&bar_full[s], (uint32_t)((c / STAGES) & 1));
+    const double* As = reinterpret_cast<const double*>(smem_raw + (size_t)s * D::STAGE_BYTES);
+    const double* Xs = reinterpret_cast<const double*>(smem_raw + (size_t)s * D::STAGE_BYTES + D::A_BYTES);
+    if (active) {
+#pragma unroll
+      for (int k0 = 0; k0 < KC; k0 += 4) {
+        double a[2], b[NB];
+#pragma unroll
+        for (int mb = 0; mb < 2; ++mb) a[mb] = As[(k0 + t) * TRP + warp * 16 + mb * 8 + g];
+#pragma unroll
+        for (int nb = 0; nb < NB; ++nb) b[nb] = Xs[(k0 + t) * KP + nb * 8 + g];
+#pragma unroll
+        for (int mb = 0; mb < 2; ++mb)
+#pragma unroll
+          for (int nb = 0; nb < NB; ++nb) dmma_884(acc[mb][nb], a[mb], b[nb]);
+      }
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&bar_empty[s]);
+  }
+  if (active) {
+#pragma unroll
+    for (int mb = 0; mb < 2; ++mb) {
+      const int r = row0 + warp * 16 + mb * 8 + g;
+#pragma unroll
+      for (int nb = 0; nb < NB; ++nb) {
+        Pack<double, 2> o;
+        o.v[0] = acc[mb][nb][0];
+        o.v[1] = acc[mb][nb][1];
+        *reinterpret_cast<Pack<double, 2>*>(Y + (size_t)r * K + nb * 8 + 2 * t) = o;
+      }
+    }
+  }
+}
+
+template <int K, int RPT>
+static int launch_dense_dmma_rpt(const slq_op* op, const double* X, double* Y, cudaStream_t st) {
+  using D = DmmaTiling<K, RPT>;
+  static DeviceOnce once;
+  if (once.needed()) {
+    SLQ_CUDA(cudaFuncSetAttribute(k_dense_dmma<K, RPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)D::SMEM_BYTES));
+    once.done();
+  }
+  k_dense_dmma<K, RPT><<<(unsigned)((op->n + D::TR - 1) / D::TR), D::NTD, D::SMEM_BYTES, st>>>((int)op->n, (const double*)op->dense, op->ld,
+                                                                                               X, Y);
+  SLQ_LAUNCH_CHECK();
+  return SLQ_OK;
+}
+
+// SLQ_DENSE=fma keeps the scalar-FMA kernel for fp64 too (A/B timing and parity of the two summation orders).
+static bool use_dmma() {
+  static int cached = -1;
+  if (cached < 0) {
+    const char* e = getenv("SLQ_DENSE");
+    cached = (e && strcmp(e, "fma") == 0) ? 0 : 1;
+  }
+  return cached == 1;
+}
+
 template <typename T, int K>
 static bool dense_tma_ok(const slq_op* op, const T* X, const T* Y) {
   using D = DenseTiling<T, K>;
@@ -170,6 +308,21 @@ static int launch_dense_tma(const slq_op* op, const T* X, T* Y, cudaStream_t st)
   }
   const char* e = getenv("SLQ_DENSE_RPT");  // A/B timing only
   if (e && atoi(e) >= 6 && atoi(e) <= 8) best = atoi(e);
+  if constexpr (sizeof(T) == 8) {
+    if (use_dmma()) {  // fp64: tensor-core tiles, one 16-row slab per consumer warp (TR = 16 RPT as below)
+      // one tall CTA per SM (224 rows: 1.8 KB contiguous per bulk copy) when that balances at least as well
+      const int64_t tall = (op->n + 223) / 224;
+      int pick = best;
+      if (((tall + sms - 1) / sms) * 14 <= best_cost) pick = 14;
+      if (e && (atoi(e) == 14 || (atoi(e) >= 6 && atoi(e) <= 8))) pick = atoi(e);
+      if (pick == 14) return launch_dense_dmma_rpt<K, 14>(op, (const double*)X, (double*)Y, st);
+      switch (best) {
+        case 6: return launch_dense_dmma_rpt<K, 6>(op, (const double*)X, (double*)Y, st);
+        case 7: return launch_dense_dmma_rpt<K, 7>(op, (const double*)X, (double*)Y, st);
+        default: return launch_dense_dmma_rpt<K, 8>(op, (const double*)X, (double*)Y, st);
+      }
+    }
+  }
   switch (best) {
     case 6: return launch_dense_tma_rpt<T, K, 6>(op, X, Y, st);
     case 7: return launch_dense_tma_rpt<T, K, 7>(op, X, Y, st);
