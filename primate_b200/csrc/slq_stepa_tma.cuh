@@ -377,6 +377,17 @@ __global__ void __launch_bounds__(TmaTiling<T, K, LONGROWS>::NTHREADS, 1)
           for (int r = 0; r < R; ++r)
 #pragma unroll
             for (int q = 0; q < V; ++q) a2[r][q] = acc[g * R + r][q];
+          // replay: the Y rows this thread updates are requested BEFORE the gathers, so their DRAM latency hides behind them
+          Pack<T, V> yrow[REPLAY ? R : 1];
+          if constexpr (REPLAY) {
+            if (last && !rp.first) {
+#pragma unroll
+              for (int r = 0; r < R; ++r) {
+                const int rl = (g * R + r) * RPP + rloc;
+                if (row0 + rl < n) yrow[r] = ld_pack<T, V, LD_STREAM>(reinterpret_cast<const T*>(rp.Y) + (size_t)(row0 + rl) * K + slot);
+              }
+            }
+          }
           tma_gather_rows<T, K, V, U, R, TILE>(a2, s, e, s_ci, s_va, s_uc, row0, uc, slot);
 #pragma unroll
           for (int r = 0; r < R; ++r)
@@ -399,8 +410,7 @@ __global__ void __launch_bounds__(TmaTiling<T, K, LONGROWS>::NTHREADS, 1)
                   const Pack<T, V> qcr = *reinterpret_cast<const Pack<T, V>*>(s_uc + (size_t)rl * K + slot);
                   if constexpr (REPLAY) {
                     // v = (A u_c) r_c - beta_j r_p u_p - alpha_j r_c u_c in the arithmetic of step A + axpy;  Y += yc v
-                    Pack<T, V> yv;
-                    if (!rp.first) yv = ld_pack<T, V, LD_STREAM>(reinterpret_cast<const T*>(rp.Y) + off);
+                    Pack<T, V> yv = yrow[REPLAY ? r : 0];
 #pragma unroll
                     for (int q = 0; q < V; ++q) {
                       const T t1 = fnma_rn(s_brp[slot + q], pv.v[q], mul_rn(a2[r][q], s_rc[slot + q]));
@@ -528,6 +538,16 @@ __global__ void __launch_bounds__(TmaTiling<T, K, LONGROWS>::NTHREADS, 1)
         }
         asm volatile("bar.sync 1, %0;" ::"n"(C::CT) : "memory");
         if (last) {
+          Pack<T, V> ytile[REPLAY ? PASSES : 1];
+          if constexpr (REPLAY) {
+            if (!rp.first) {
+#pragma unroll
+              for (int ps = 0; ps < PASSES; ++ps) {
+                const int rl = ps * RPP + rloc;
+                if (row0 + rl < n) ytile[ps] = ld_pack<T, V, LD_STREAM>(reinterpret_cast<const T*>(rp.Y) + (size_t)(row0 + rl) * K + slot);
+              }
+            }
+          }
 #pragma unroll
           for (int ps = 0; ps < PASSES; ++ps) {
             const int rl = ps * RPP + rloc;
@@ -547,8 +567,7 @@ __global__ void __launch_bounds__(TmaTiling<T, K, LONGROWS>::NTHREADS, 1)
                 if (HAS_UP) pv = *reinterpret_cast<const Pack<T, V>*>(s_up + (size_t)rl * K + slot);
                 const Pack<T, V> qcr = *reinterpret_cast<const Pack<T, V>*>(s_uc + (size_t)rl * K + slot);
                 if constexpr (REPLAY) {
-                  Pack<T, V> yv;
-                  if (!rp.first) yv = ld_pack<T, V, LD_STREAM>(reinterpret_cast<const T*>(rp.Y) + off);
+                  Pack<T, V> yv = ytile[REPLAY ? ps : 0];
 #pragma unroll
                   for (int q = 0; q < V; ++q) {
                     const T t1 = fnma_rn(s_brp[slot + q], pv.v[q], mul_rn(av.v[q], s_rc[slot + q]));

@@ -19,7 +19,9 @@ from .special import param_callable
 from .tridiag import eigh_tridiag  # noqa: F401
 
 F64: np.dtype = np.dtype("float64")
-_FORCE_STORED_BASIS = False  # tests / A-B timing: route orth = 0 through the stored-basis formula too
+BASIS_BUDGET = 40 << 30  # bytes a stored Lanczos basis (deg x n x k) may take before f(A) X goes basis-free
+_FORCE_STORED_BASIS = False  # tests / A-B timing: route every f(A) X through the stored-basis formula
+_FORCE_TWOPASS = False  # ... or (orth = 0) through the basis-free two-pass engine
 
 
 def _op_checks(A: Any) -> list:
@@ -52,6 +54,8 @@ class MatrixFunction(LinearOperator):
 		orth: number of Lanczos vectors to re-orthogonalise against per step.
 		dtype: float64 or float32.
 		kwargs: parameters of the built-in function (t, a, b, threshold, q).
+		basis (keyword, not in the reference): engine behind `M @ X` -- "auto" (default), "stored" (the reference's
+			n x deg Lanczos basis), or "twopass" (basis-free: memory independent of deg; orth = 0 only).
 		comm (keyword, not in the reference): None (default) keeps block products on this process; "auto" or a
 			torch.distributed group splits the columns of every block product / quadratic form over the ranks (the
 			operator is replicated per GPU; all ranks must then make the same calls; see `sharding.sharded_columns`).
@@ -61,6 +65,8 @@ class MatrixFunction(LinearOperator):
 		assert is_linear_op(A), "Invalid operator `A`; must be dim=2 symmetric operator with defined matvec"
 		assert deg >= 2, "Degree must be >= 2"
 		comm = kwargs.pop("comm", None)
+		self._basis = kwargs.pop("basis", "auto")  # f(A) X engine: "auto" | "stored" | "twopass" (see _use_twopass)
+		assert self._basis in ("auto", "stored", "twopass")
 		super().__init__(dtype=np.dtype(dtype), shape=tuple(A.shape))  # SciPy >= 1.12 needs this for `M @ v`
 		if fun is None or isinstance(fun, str):
 			host_fun = param_callable(fun, **dict(kwargs)) if isinstance(fun, str) else (lambda x: x)
@@ -165,7 +171,7 @@ class MatrixFunction(LinearOperator):
 		orth = 0: the basis-free two-pass engine (X is left intact; memory independent of `deg`).  orth > 0: the
 		reference's stored-basis formula y = ||x|| Q Y f(Theta) Y^T e_1 (operators.py:102-124; X is clobbered)."""
 		torch = engine._torch()
-		if self._orth == 0 and not _FORCE_STORED_BASIS:
+		if self._use_twopass(self.shape[0]):
 			if self._fun_spec is not None:
 				fid, prm = self._fun_spec
 				return self.device_op.funm_matmat(X, self._deg, self._rtol, fid, prm)
@@ -185,11 +191,24 @@ class MatrixFunction(LinearOperator):
 		return self.device_op._from_internal(Y)  # the basis was combined in the operator's row order
 
 	# ---- device-panel API (block drivers that keep their panels on the GPU) -----------------------------------------
-	def _basis_block_width(self, n: int, budget: int = 40 << 30) -> int:
-		"""Widest probe block (power of two <= 32) for f(A) X: the two-pass engine (orth = 0) holds five panels whatever
-		`deg` is; the stored-basis path (orth > 0) is narrowed until its deg x n x k basis stays within `budget` bytes."""
+	def _use_twopass(self, n: int) -> bool:
+		"""f(A) X policy.  Both engines move about the same bytes per column and step (stored basis: CSR/k + 9 panel
+		passes; two-pass: 2 CSR/k + 11), so the stored basis -- one Lanczos sweep -- is kept while a basis of at least 4
+		columns fits in `BASIS_BUDGET` (measured at config C5, 64 columns: 1.74 s stored at k = 4 vs 1.94 s two-pass at
+		k = 32); beyond that, and whenever the caller asks (`basis="twopass"`), the basis-free engine takes over: its
+		memory is five panels whatever `deg` is.  orth > 0 needs the stored vectors for the re-projection."""
+		if self._orth != 0 or _FORCE_STORED_BASIS or self._basis == "stored":
+			return False
+		if _FORCE_TWOPASS or self._basis == "twopass":
+			return True
+		return 4 * self._deg * n * np.dtype(self.dtype).itemsize > BASIS_BUDGET
+
+	def _basis_block_width(self, n: int, budget: Optional[int] = None) -> int:
+		"""Widest probe block (power of two <= 32) for f(A) X: the two-pass engine holds five panels whatever `deg` is;
+		the stored-basis path is narrowed until its deg x n x k basis stays within the budget."""
+		budget = BASIS_BUDGET if budget is None else budget
 		itemsize = np.dtype(self.dtype).itemsize
-		per_column = (5 if (self._orth == 0 and not _FORCE_STORED_BASIS) else self._deg) * n * itemsize
+		per_column = (5 if self._use_twopass(n) else self._deg) * n * itemsize
 		k = 32
 		while k > 1 and k * per_column > budget:
 			k >>= 1

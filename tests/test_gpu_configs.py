@@ -212,8 +212,8 @@ def _laplacian_3d(g):
 
 
 def test_C5_laplacian3d_inverse_quad_and_matvec(oracle):
-	"""f = inv, deg 80 on the 48^3 7-point Laplacian: quadratic forms (1e-8) and f(A) x through the basis-free two-pass
-	engine (1e-8 of ||y||) vs the reference's stored-basis formula (operators.py:102-151)."""
+	"""f = inv, deg 80 on the 48^3 7-point Laplacian: quadratic forms (1e-8) and f(A) x through both engines -- basis-free
+	two-pass and stored basis -- (1e-8 of ||y||) vs the reference's stored-basis formula (operators.py:102-151)."""
 	from primate_b200.operators import MatrixFunction
 
 	A = _laplacian_3d(48)
@@ -225,10 +225,12 @@ def test_C5_laplacian3d_inverse_quad_and_matvec(oracle):
 		ry = oracle.ref_quad(A, W[:, p], "inv", deg=deg, orth=0)[0]
 		assert abs(y[p] / ry - 1) < 1e-8
 	V = W[:, :3]
-	Y = M @ V
+	Y = MatrixFunction(A, "inv", deg=deg, orth=0, basis="twopass") @ V
+	Ys = MatrixFunction(A, "inv", deg=deg, orth=0, basis="stored") @ V
 	for j in (0, 2):
 		ref = oracle.ref_matvec(A, V[:, j], "inv", deg=deg, orth=0)
 		assert np.max(np.abs(Y[:, j] - ref)) < 1e-8 * np.linalg.norm(ref)
+		assert np.max(np.abs(Ys[:, j] - ref)) < 1e-8 * np.linalg.norm(ref)
 	assert np.max(np.abs(np.ravel(M._matvec(V[:, 1])) - Y[:, 1])) < 1e-10 * np.linalg.norm(Y[:, 1])
 	# A (A^-1 x) = x up to the Krylov truncation error of deg 80 on a grid of diameter 141
 	resid = np.linalg.norm(A @ Y[:, 0] - V[:, 0]) / np.linalg.norm(V[:, 0])

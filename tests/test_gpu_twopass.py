@@ -14,18 +14,12 @@ def _both(A, fun, deg, X, dtype=np.float64, **kw):
 	"""(two-pass, stored-basis) results of M @ X on the device for the same host panel X."""
 	import torch
 
-	from primate_b200 import operators
 	from primate_b200.operators import MatrixFunction
 
-	M = MatrixFunction(A, fun, deg=deg, orth=0, dtype=dtype, **kw)
 	Xd = torch.from_numpy(np.ascontiguousarray(X, dtype=dtype)).cuda()
-	y2 = M.matmat_device(Xd).cpu().numpy()
+	y2 = MatrixFunction(A, fun, deg=deg, orth=0, dtype=dtype, basis="twopass", **kw).matmat_device(Xd).cpu().numpy()
 	assert np.array_equal(Xd.cpu().numpy(), np.asarray(X, dtype=dtype))  # start panel left intact
-	operators._FORCE_STORED_BASIS = True
-	try:
-		y1 = M.matmat_device(Xd).cpu().numpy()
-	finally:
-		operators._FORCE_STORED_BASIS = False
+	y1 = MatrixFunction(A, fun, deg=deg, orth=0, dtype=dtype, basis="stored", **kw).matmat_device(Xd).cpu().numpy()
 	return y2, y1
 
 
@@ -39,7 +33,7 @@ def test_twopass_matches_reference_goldens_dense(golden, fun, kw):
 	from primate_b200.operators import MatrixFunction
 
 	A, v = golden["A150"], golden["v42"]
-	M = MatrixFunction(A, fun, deg=20, orth=0, **kw)
+	M = MatrixFunction(A, fun, deg=20, orth=0, basis="twopass", **kw)
 	y = np.ravel(M._matvec(v.copy()))
 	g = np.ravel(golden[f"matvec_{fun}_orth0_v42"])
 	assert np.max(np.abs(y - g)) < 1e-8 * np.max(np.abs(g))
@@ -63,7 +57,7 @@ def test_twopass_long_rows_and_row_orders(reorder):
 	"""Hub rows (the non-zero-balanced fused variant) and both internal row orders: results in the caller's order."""
 	import torch
 
-	from primate_b200 import engine, operators
+	from primate_b200 import engine
 	from primate_b200.operators import MatrixFunction
 
 	rng = np.random.default_rng(2)
@@ -77,15 +71,10 @@ def test_twopass_long_rows_and_row_orders(reorder):
 	A.sort_indices()
 	assert np.diff(A.indptr).max() > 64
 	op = engine.DeviceOperator(A, reorder=reorder)
-	M = MatrixFunction(op, "sqrt", deg=25, orth=0)
 	X = rng.standard_normal((n, 16))
 	Xd = torch.from_numpy(X).cuda()
-	y2 = M.matmat_device(Xd).cpu().numpy()
-	operators._FORCE_STORED_BASIS = True
-	try:
-		y1 = M.matmat_device(Xd).cpu().numpy()
-	finally:
-		operators._FORCE_STORED_BASIS = False
+	y2 = MatrixFunction(op, "sqrt", deg=25, orth=0, basis="twopass").matmat_device(Xd).cpu().numpy()
+	y1 = MatrixFunction(op, "sqrt", deg=25, orth=0, basis="stored").matmat_device(Xd).cpu().numpy()
 	assert np.max(np.abs(y2 - y1)) <= 1e-12 * np.max(np.abs(y1))
 	ew, U = np.linalg.eigh(A.toarray())
 	ref = (U * np.sqrt(ew)) @ (U.T @ X[:, :2])
@@ -106,14 +95,14 @@ def test_twopass_early_break_and_host_callable(golden):
 	rng = np.random.default_rng(0)
 	X = rng.standard_normal((n, 8))
 	for fun in ("exp", lambda x: np.exp(x)):
-		M = MatrixFunction(A, fun, deg=12, orth=0)
+		M = MatrixFunction(A, fun, deg=12, orth=0, basis="twopass")
 		Y = M.matmat_device(torch.from_numpy(X).cuda()).cpu().numpy()
 		assert np.all(np.isfinite(Y))
 		assert np.max(np.abs(Y - np.exp(d)[:, None] * X)) < 1e-9 * np.max(np.abs(Y))
 	A30 = _L30(golden)
 	V = rng.standard_normal((900, 5))
-	y_builtin = MatrixFunction(A30, "exp", deg=30, orth=0, t=-0.3).matmat_device(torch.from_numpy(V).cuda()).cpu().numpy()
-	y_callable = MatrixFunction(A30, lambda x: np.exp(-0.3 * x), deg=30, orth=0).matmat_device(torch.from_numpy(V).cuda()).cpu().numpy()
+	y_builtin = MatrixFunction(A30, "exp", deg=30, orth=0, t=-0.3, basis="twopass").matmat_device(torch.from_numpy(V).cuda()).cpu().numpy()
+	y_callable = MatrixFunction(A30, lambda x: np.exp(-0.3 * x), deg=30, orth=0, basis="twopass").matmat_device(torch.from_numpy(V).cuda()).cpu().numpy()
 	assert np.max(np.abs(y_builtin - y_callable)) <= 1e-11 * np.max(np.abs(y_builtin))
 
 
@@ -132,3 +121,23 @@ def test_twopass_fp32_and_dense_tiled():
 	ew, U = np.linalg.eigh(D)
 	ref = (U * np.log(ew)) @ (U.T @ Xd)
 	assert np.max(np.abs(y2 - ref)) < 1e-6 * np.max(np.abs(ref))
+
+
+def test_auto_policy_goes_basis_free_when_the_basis_would_not_fit(golden, monkeypatch):
+	"""`basis="auto"`: stored basis while 4 columns of it fit in the budget, the two-pass engine beyond (here the budget is
+	shrunk instead of the problem grown); both give the same f(A) X."""
+	import torch
+
+	from primate_b200 import operators
+	from primate_b200.operators import MatrixFunction
+
+	A = _L30(golden)
+	M = MatrixFunction(A, "exp", deg=30, orth=0, t=-0.3)
+	assert not M._use_twopass(900) and M._basis_block_width(900) == 32
+	X = torch.from_numpy(np.random.default_rng(0).standard_normal((900, 8))).cuda()
+	y_stored = M.matmat_device(X).cpu().numpy()
+	monkeypatch.setattr(operators, "BASIS_BUDGET", 4 * 30 * 900 * 8 - 1)
+	assert M._use_twopass(900) and M._basis_block_width(900) == 32
+	y_two = M.matmat_device(X).cpu().numpy()
+	assert np.max(np.abs(y_two - y_stored)) <= 1e-12 * np.max(np.abs(y_stored))
+	assert not MatrixFunction(A, "exp", deg=30, orth=3)._use_twopass(900)  # re-orthogonalisation needs the stored vectors
