@@ -119,6 +119,43 @@ def _balance_rows_device(rowptr, colidx, vals, n: int, tile: int):
 	return nrp.int(), ncol, nval, perm.int()
 
 
+def _device_csr_from(A, dtype, dev):
+	"""COO or BSR SciPy matrix -> (rowptr, colidx, vals) int32/int32/float device tensors with sorted, de-duplicated
+	(summed, as SciPy's tocsr() does) column indices; the conversion runs on the GPU (index bookkeeping with torch: a
+	radix sort on row*n + col keys and a segmented sum), only the raw format arrays cross PCIe.  Returns the bytes uploaded."""
+	torch = _torch()
+	n = int(A.shape[0])
+	tdt = _tdtype(dtype)
+	if A.format == "coo":
+		r = torch.from_numpy(np.ascontiguousarray(A.row, dtype=np.int64)).to(dev)
+		c = torch.from_numpy(np.ascontiguousarray(A.col, dtype=np.int64)).to(dev)
+		v = torch.from_numpy(np.ascontiguousarray(A.data, dtype=np.dtype(dtype))).to(dev)
+		up = A.row.nbytes + A.col.nbytes + A.data.nbytes
+	else:  # bsr: block (bi, bj) at position p holds A[bi R + a, bj C + b] = data[p, a, b]
+		R, Cb = A.blocksize
+		ip = torch.from_numpy(np.ascontiguousarray(A.indptr, dtype=np.int64)).to(dev)
+		bj = torch.from_numpy(np.ascontiguousarray(A.indices, dtype=np.int64)).to(dev)
+		blocks = torch.from_numpy(np.ascontiguousarray(A.data, dtype=np.dtype(dtype))).to(dev)
+		up = A.indptr.nbytes + A.indices.nbytes + A.data.nbytes
+		bi = torch.repeat_interleave(torch.arange(ip.numel() - 1, device=dev), ip[1:] - ip[:-1])
+		a = torch.arange(R, device=dev).view(1, R, 1)
+		b = torch.arange(Cb, device=dev).view(1, 1, Cb)
+		r = (bi.view(-1, 1, 1) * R + a).expand(-1, R, Cb).reshape(-1)
+		c = (bj.view(-1, 1, 1) * Cb + b).expand(-1, R, Cb).reshape(-1)
+		v = blocks.reshape(-1)
+	key, order = torch.sort(r * n + c)
+	v = v[order].to(tdt)
+	uniq, inverse = torch.unique_consecutive(key, return_inverse=True)
+	vals = torch.zeros(uniq.numel(), dtype=tdt, device=dev).index_add_(0, inverse, v)
+	if A.format == "bsr":  # SciPy keeps explicit zeros of stored blocks; so do we (same operator either way)
+		pass
+	rows = uniq // n
+	rowptr = torch.zeros(n + 1, dtype=torch.int64, device=dev)
+	rowptr[1:] = torch.cumsum(torch.bincount(rows, minlength=n), 0)
+	assert uniq.numel() < 2**31 - 1, "nnz must fit int32"
+	return rowptr.int(), (uniq % n).int(), vals, int(up)
+
+
 class _DevView:
 	"""Exposes a raw device pointer through __cuda_array_interface__ so torch can view it without a copy."""
 
@@ -168,8 +205,28 @@ class DeviceOperator:
 		self._handle = ctypes.c_void_p()
 		self.h2d_bytes = 0
 		dev = torch.device("cuda", torch.cuda.current_device())
-		if sp.issparse(A):
-			C = A.tocsr()
+		if sp.issparse(A) and A.format in ("coo", "bsr") and not (isinstance(reorder, int) and not isinstance(reorder, bool) and reorder > 1) \
+				and reorder is not True and not _want_reorder(reorder, self.n, int(A.nnz)):
+			# COO / BSR: the raw arrays are uploaded as they are and turned into sorted CSR ON THE DEVICE (no host tocsr())
+			rowptr, colidx, vals, up = _device_csr_from(A, self.dtype, dev)
+			self.h2d_bytes = up
+			self.perm = None
+			lens = rowptr[1:] - rowptr[:-1]
+			if isinstance(reorder, str) and reorder == "balance":
+				rowptr, colidx, vals, self.perm = _balance_rows_device(rowptr, colidx, vals, self.n, REORDER_TILE)
+			self._keep = [rowptr, colidx, vals]
+			self.kind, self.nnz = "csr", int(colidx.numel())
+			_ffi.check(L.slq_csr_create_ex(self.n, self.nnz, rowptr.data_ptr(), colidx.data_ptr(), vals.data_ptr(), self.code,
+			                               int(lens.max().item()) if self.n else 0, None, ctypes.byref(self._handle)))  # fmt: skip
+		elif sp.issparse(A):
+			if A.format == "csc":
+				# a symmetric matrix in CSC form IS its CSR form (A^T = A): no conversion, exactly the arrays the reference's
+				# pybind11 caster hands to Eigen (_lanczos.cpp:89-93)
+				C = sp.csr_matrix((A.data, A.indices, A.indptr), shape=A.shape, copy=False)
+				if not A.has_sorted_indices:
+					C = C.copy()
+			else:
+				C = A.tocsr()
 			C.sort_indices()
 			assert C.nnz < 2**31 - 1, "nnz must fit int32"
 			ip = np.ascontiguousarray(C.indptr, dtype=np.int32)

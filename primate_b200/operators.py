@@ -165,6 +165,23 @@ class MatrixFunction(LinearOperator):
 			C[p] = Y @ (np.ravel(self._fun(th[p])) * Y[0, :])
 		return torch.from_numpy(C).cuda()
 
+	def nodes_range(self, stream, first: int, count: int, kmax: int = 64):
+		"""Gauss quadrature rules of probes [first, first + count) of a `ProbeStream`: device tensors theta, tau of shape
+		(count, deg) -- Ritz values and weights of every probe, the raw material of spectral densities / moments
+		(src/primate/lanczos.py:120-164 and the reference's planned `spectral_density`) -- and ||x||^2 (count,).  The
+		Lanczos blocks run back to back; ONE batched Golub-Welsch launch (a warp per Jacobi matrix) follows."""
+		torch = engine._torch()
+		tdt = engine._tdtype(self.dtype)
+		alpha = torch.empty((count, self._deg + 1), dtype=tdt, device="cuda")
+		beta = torch.empty((count, self._deg + 1), dtype=tdt, device="cuda")
+		xnorm2 = torch.empty(count, dtype=torch.float64, device="cuda")
+		op, ncv = self.device_op, max(2, self._orth)
+		for off, k in _offsets(engine.block_sizes(count, kmax)):
+			out = {"alpha": alpha[off : off + k], "beta": beta[off : off + k], "xnorm2": xnorm2[off : off + k]}
+			op.lanczos(stream.block(k, first + off), self._deg, self._rtol, self._orth, ncv, out=out)
+		theta, tau, _, info = engine.quadrature(alpha, beta, self._deg, fun_id=-1)
+		return theta, tau, xnorm2
+
 	def matmat_block(self, X):
 		"""f(A) X for a device probe block X (n, k) -> device block (n, k).
 

@@ -259,3 +259,60 @@ def test_device_csr_operator_matches_host_ingestion(golden):
 		assert np.allclose(op.matvec(x), A @ x, rtol=1e-13, atol=1e-13)
 		est = hutch(MatrixFunction(op, "exp", deg=20, orth=0), converge="count", count=64, seed=3)
 		assert abs(est / ref - 1) < 1e-10
+
+
+def test_ingestion_formats_without_host_conversion(golden):
+	"""CSC is taken as it is (a symmetric CSC matrix is its own CSR), COO and BSR are converted on the device: SpMM and
+	Lanczos coefficients equal the CSR ingestion path; COO duplicates are summed as SciPy's tocsr() does."""
+	from primate_b200 import engine
+
+	A = _L30(golden)
+	n = A.shape[0]
+	X = np.random.default_rng(0).standard_normal((n, 8))
+	ref = A @ X
+	base = engine.DeviceOperator(A, reorder=False)
+	o0 = base.lanczos(engine.block_from_columns(X, np.float64), 12, 1e-8, 0, 2)
+	coo = A.tocoo()
+	perm = np.random.default_rng(1).permutation(coo.nnz)
+	dup = sp.coo_matrix((np.concatenate([coo.data[perm] * 0.25, coo.data[perm] * 0.75]), (np.tile(coo.row[perm], 2), np.tile(coo.col[perm], 2))), shape=A.shape)
+	B = sp.kron(A[:300, :300], np.array([[2.0, 1.0, 0.0], [1.0, 2.0, 1.0], [0.0, 1.0, 2.0]])).tobsr(blocksize=(3, 3))
+	for M in (A.tocsc(), coo, dup, A.tobsr(blocksize=(2, 2))):
+		op = engine.DeviceOperator(M, reorder=False)
+		assert op.nnz == A.nnz or M.format == "bsr"
+		Y = op.matmat(engine.block_from_columns(X, np.float64)).cpu().numpy()
+		assert np.max(np.abs(Y - ref)) < 1e-12 * np.max(np.abs(ref)), M.format
+		o = op.lanczos(engine.block_from_columns(X, np.float64), 12, 1e-8, 0, 2)
+		assert rel_err(o["alpha"].cpu().numpy()[:, :12], o0["alpha"].cpu().numpy()[:, :12]) < 1e-11
+	opb = engine.DeviceOperator(B, reorder=False)
+	Xb = np.random.default_rng(2).standard_normal((900, 4))
+	assert np.max(np.abs(opb.matmat(engine.block_from_columns(Xb, np.float64)).cpu().numpy() - B @ Xb)) < 1e-11
+
+
+def test_spectral_nodes_and_density(golden, oracle):
+	"""Per-probe Gauss rules from the device (theta, tau for every probe of a range) equal Lanczos + LAPACK on the same
+	probes; the smoothed density integrates to one and its moments match tr(A^j) / n."""
+	from primate_b200.integrate import spectral_density
+	from primate_b200.operators import MatrixFunction
+	from primate_b200.random import ProbeStream, isotropic
+
+	A = golden["A150"]
+	M = MatrixFunction(A, "identity", deg=20, orth=0)
+	theta, tau, xn = M.nodes_range(ProbeStream(150, "rademacher", seed=4), 0, 40)
+	theta, tau = theta.cpu().numpy(), tau.cpu().numpy()
+	W = isotropic((150, 40), seed=4)
+	for p in (0, 17, 39):
+		a, b, _ = oracle.ref_lanczos(A, W[:, p], 20, 1e-8, 0)
+		th, ta = oracle.ref_quadrature(a, b, 20)
+		assert np.max(np.abs(theta[p] - th)) < 1e-12 and np.max(np.abs(tau[p] - ta)) < 1e-11
+	assert np.allclose(xn.cpu().numpy(), 150.0)
+	g = np.random.default_rng(4)
+	t, dens, th2, ta2 = spectral_density(A, deg=20, count=40, points=400, seed=g, full=True)
+	assert np.array_equal(th2, theta) and np.array_equal(ta2, tau)
+	chk = np.random.default_rng(4)
+	chk.bit_generator.advance(40 * 150)
+	assert g.bit_generator.state == chk.bit_generator.state
+	assert abs(np.trapezoid(dens, t) - 1.0) < 1e-3
+	ew = np.linalg.eigvalsh(A)
+	for j in (1, 2):  # moments of the quadrature measure: E[x^T A^j x] / n = tr(A^j) / n
+		mom = float((tau * theta**j).sum(axis=1).mean())
+		assert abs(mom - (ew**j).mean()) < 0.05 * (ew**j).mean()
