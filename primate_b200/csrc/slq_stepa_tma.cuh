@@ -51,6 +51,16 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src, uint32
                : "memory");
 }
 
+// 16-byte asynchronous gather global -> shared (L2 only: the gathered probe rows are not re-used from L1)
+__device__ __forceinline__ void cp_async16(void* dst_smem, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst_smem)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
 #ifndef SLQ_TMA_U
 #define SLQ_TMA_U 5  // gathers per row per round
 #endif
@@ -84,10 +94,16 @@ struct TmaTiling {
   static constexpr int PASSES = TILE / RPP;
   static constexpr int R = PASSES % SLQ_TMA_R == 0 ? SLQ_TMA_R : 1;  // rows per thread processed together
   static constexpr size_t PANEL = (size_t)TILE * K * sizeof(T);
-  static constexpr size_t BAL_EXTRA = PANEL + (size_t)RPP * 4 + 16;  // balanced variant: row sums + continuation rows
-  static constexpr size_t BAL_BUDGET = 200 * 1024;
+  // Balanced variant (irregular operators): no staged u_c / u_p tiles (on a power-law graph next to no column is
+  // tile-local); the shared memory goes to a ring of RING 16-byte slots PER CONSUMER THREAD instead, filled by
+  // cp.async gathers that run RING non-zeros ahead of the FMAs -- bytes in flight are bounded by shared memory
+  // (RING x 480 x 16 B = 120 KB per SM), not by the 128-register budget (8 x 16 B per thread before).
+  static constexpr int RING = 16;
+  static constexpr size_t RING_BYTES = (size_t)RING * CT * 16;
+  static constexpr size_t BAL_EXTRA = PANEL + RING_BYTES + (size_t)RPP * 4 + 32;  // row sums + gather ring + continuation rows
+  static constexpr size_t BAL_BUDGET = 216 * 1024;
   static constexpr bool bal_fits(int cap, int stages) {
-    return (size_t)stages * (2 * PANEL + (size_t)cap * (sizeof(T) + 4) + 1024) + BAL_EXTRA <= BAL_BUDGET;
+    return (size_t)stages * ((size_t)cap * (sizeof(T) + 4) + 1024) + BAL_EXTRA <= BAL_BUDGET;
   }
   // balanced variant: the chunk is the unit of the per-chunk barriers and of the slice bookkeeping, so as large as fits
   static constexpr int BAL_CAP = bal_fits(3840, 2) ? 3840 : (bal_fits(1920, 2) ? 1920 : 960);
@@ -97,9 +113,10 @@ struct TmaTiling {
   static constexpr int NRP = (TILE + 1 + 31) / 32;     // row pointers per producer lane
   static constexpr int RP_LEN = NRP * 32;
   // stage layout (bytes)
+  static constexpr size_t STAGED_PANEL = BAL ? 0 : (size_t)TILE * K * sizeof(T);
   static constexpr size_t OFF_UC = 0;
-  static constexpr size_t OFF_UP = OFF_UC + (size_t)TILE * K * sizeof(T);
-  static constexpr size_t OFF_VA = OFF_UP + (size_t)TILE * K * sizeof(T);
+  static constexpr size_t OFF_UP = OFF_UC + STAGED_PANEL;
+  static constexpr size_t OFF_VA = OFF_UP + STAGED_PANEL;
   static constexpr size_t OFF_CI = OFF_VA + (size_t)CAP * sizeof(T);
   static constexpr size_t OFF_RP = OFF_CI + (size_t)CAP * 4;
   static constexpr size_t OFF_HDR = OFF_RP + (size_t)RP_LEN * 4;
@@ -199,6 +216,7 @@ __global__ void __launch_bounds__(TmaTiling<T, K, LONGROWS>::NTHREADS, 1)
   unsigned char* const base = smem_raw;  // bulk copies need 16-byte alignment only
   T* const s_acc = reinterpret_cast<T*>(smem_raw + (size_t)STAGES * C::STAGE_BYTES);  // balanced variant: TILE x K row sums
   int* const s_crow = reinterpret_cast<int*>(s_acc + (size_t)TILE * K);                // ... and one continuation row per group
+  unsigned char* const s_ring = reinterpret_cast<unsigned char*>(s_crow) + (((size_t)RPP * 4 + 16 + 15) / 16) * 16;  // gather ring
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
   if (tid == 0) {
@@ -243,13 +261,16 @@ __global__ void __launch_bounds__(TmaTiling<T, K, LONGROWS>::NTHREADS, 1)
     // Once the index slice of a stage has landed, touch the probe rows it points at with prefetch.global.L2: the one
     // first-touch (DRAM) gather per matrix row then costs the consumers an L2 hit instead of a full DRAM round trip.
     auto prefetch_stage = [&]() {
-      if (pf_stage < 0 || !(SLQ_TMA_PREFETCH || LONGROWS)) return;  // irregular operators: gathers are mostly off-tile
+      // (Round 1 ran this for the irregular variant; a folded-column experiment -- every gather an L2 hit, same kernel
+      // time -- showed the single producer warp spending ~30k cycles per chunk issuing 3840 scattered prefetches and
+      // thereby gating the whole CTA: profiles/r02_c3_experiments.md.  The consumers' cp.async ring hides that latency.)
+      if (pf_stage < 0 || !SLQ_TMA_PREFETCH) return;
       mbar_wait(&bar_full[pf_stage], pf_phase);
       const int* p_ci = reinterpret_cast<const int*>(base + (size_t)pf_stage * C::STAGE_BYTES + C::OFF_CI);
       constexpr int LINES = (K * (int)sizeof(T) + 127) / 128;
       for (int i = lane; i < pf_cnt * LINES; i += 32) {
         const int c = p_ci[i / LINES];
-        if ((unsigned)(c - pf_row0) < (unsigned)TILE) continue;  // staged with the tile
+        if (!LONGROWS && (unsigned)(c - pf_row0) < (unsigned)TILE) continue;  // staged with the tile
         const char* a = reinterpret_cast<const char*>(uc + (size_t)c * K) + (i % LINES) * 128;
         asm volatile("prefetch.global.L2 [%0];" ::"l"(a));
       }
@@ -300,8 +321,8 @@ __global__ void __launch_bounds__(TmaTiling<T, K, LONGROWS>::NTHREADS, 1)
         __syncwarp();
         if (lane == 0) {
           const uint32_t b_ci = (uint32_t)nb * 4u, b_va = (uint32_t)nb * (uint32_t)sizeof(T);
-          const uint32_t b_up = (HAS_UP && last) ? (uint32_t)nrows * K * (uint32_t)sizeof(T) : 0u;
-          const uint32_t b_uc = (uint32_t)nrows * K * (uint32_t)sizeof(T);  // every chunk: in-tile columns read it
+          const uint32_t b_up = (!LONGROWS && HAS_UP && last) ? (uint32_t)nrows * K * (uint32_t)sizeof(T) : 0u;
+          const uint32_t b_uc = LONGROWS ? 0u : (uint32_t)nrows * K * (uint32_t)sizeof(T);  // every chunk: in-tile columns read it
           const uint32_t total = b_ci + b_va + b_up + b_uc;
           if (total > 0) {
             mbar_arrive_expect_tx(&bar_full[stage], total);
@@ -309,7 +330,7 @@ __global__ void __launch_bounds__(TmaTiling<T, K, LONGROWS>::NTHREADS, 1)
               bulk_g2s(s_ci, colidx + lo, b_ci, &bar_full[stage]);
               bulk_g2s(s_va, vals + lo, b_va, &bar_full[stage]);
             }
-            bulk_g2s(S + C::OFF_UC, uc + (size_t)row0 * K, b_uc, &bar_full[stage]);
+            if (b_uc) bulk_g2s(S + C::OFF_UC, uc + (size_t)row0 * K, b_uc, &bar_full[stage]);
             if (b_up) bulk_g2s(S + C::OFF_UP, up + (size_t)row0 * K, b_up, &bar_full[stage]);
           } else {
             mbar_arrive(&bar_full[stage]);
@@ -495,30 +516,64 @@ __global__ void __launch_bounds__(TmaTiling<T, K, LONGROWS>::NTHREADS, 1)
             }
             *dst = x;
           };
-          // the slice is walked as a flat list, UB gathers in flight whatever the row lengths are
-          for (; i < end; i += UB) {
-            Pack<T, V> xv[UB];
+          // The slice is walked as a flat list.  Gathers run RING non-zeros ahead of the FMAs through this thread's
+          // private ring in shared memory: slot d of thread tid is the 16-byte word (d * CT + tid), so the lanes of a row
+          // group write and read adjacent words (conflict-free) and nobody else ever touches them (no barrier needed,
+          // cp.async.wait_group orders a thread's own copies).  One commit group per non-zero, empty past the end.
+          constexpr int RING = C::RING, UW = 4;  // UW non-zeros per loop trip and per commit group
+          static_assert(RING % UW == 0, "ring depth must be a multiple of the unroll");
+          unsigned char* const my_ring = s_ring + (size_t)tid * 16;
+          auto slot_ptr = [&](int d) { return my_ring + (size_t)d * C::CT * 16; };
+          int issued = i;
 #pragma unroll
-            for (int u = 0; u < UB; ++u)
-              if (i + u < end) xv[u] = tma_fetch<T, K, V, TILE>(s_ci[i + u], row0, s_uc, uc, slot);
+          for (int d = 0; d < RING; d += UW) {
 #pragma unroll
-            for (int u = 0; u < UB; ++u)
-              if (i + u < end) {
-                if (i + u >= row_end) {
-                  flush();
-                  cont = false;
-#pragma unroll
-                  for (int q = 0; q < V; ++q) part[q] = (T)0;
-                  do {
-                    ++r;
-                    row_end = min(s_rp[r + 1], hi) - lo;
-                  } while (i + u >= row_end && r < TILE - 1);  // skip empty rows
-                }
-                const T av = s_va[i + u];
-#pragma unroll
-                for (int q = 0; q < V; ++q) part[q] = fma(av, xv[u].v[q], part[q]);
-              }
+            for (int u = 0; u < UW; ++u)
+              if (issued + u < end) cp_async16(slot_ptr(d + u), uc + (size_t)s_ci[issued + u] * K + slot);
+            cp_async_commit();
+            issued += UW;
           }
+          int rs = 0;
+          for (; i < end; i += UW) {
+            cp_async_wait<RING / UW - 1>();  // the oldest group (non-zeros i .. i+UW-1) has landed
+            Pack<T, V> xv[UW];
+            T av[UW];
+#pragma unroll
+            for (int u = 0; u < UW; ++u) {
+              xv[u] = *reinterpret_cast<const Pack<T, V>*>(slot_ptr(rs + u));
+              av[u] = (i + u < end) ? s_va[i + u] : (T)0;
+            }
+            if (i + UW <= row_end && i + UW <= end) {  // common case: the whole group belongs to the open row
+#pragma unroll
+              for (int u = 0; u < UW; ++u)
+#pragma unroll
+                for (int q = 0; q < V; ++q) part[q] = fma(av[u], xv[u].v[q], part[q]);
+            } else {
+#pragma unroll
+              for (int u = 0; u < UW; ++u)
+                if (i + u < end) {
+                  if (i + u >= row_end) {
+                    flush();
+                    cont = false;
+#pragma unroll
+                    for (int q = 0; q < V; ++q) part[q] = (T)0;
+                    do {
+                      ++r;
+                      row_end = min(s_rp[r + 1], hi) - lo;
+                    } while (i + u >= row_end && r < TILE - 1);  // skip empty rows
+                  }
+#pragma unroll
+                  for (int q = 0; q < V; ++q) part[q] = fma(av[u], xv[u].v[q], part[q]);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < UW; ++u)  // refill the slots just read
+              if (issued + u < end) cp_async16(slot_ptr(rs + u), uc + (size_t)s_ci[issued + u] * K + slot);
+            cp_async_commit();
+            issued += UW;
+            rs = (rs + UW == RING) ? 0 : rs + UW;
+          }
+          cp_async_wait<0>();
           flush();
           r_last = r;
           last_is_cont = cont;
@@ -564,8 +619,8 @@ __global__ void __launch_bounds__(TmaTiling<T, K, LONGROWS>::NTHREADS, 1)
                 st_pack<T, V, true>(w + off, av);
               } else {
                 Pack<T, V> pv;
-                if (HAS_UP) pv = *reinterpret_cast<const Pack<T, V>*>(s_up + (size_t)rl * K + slot);
-                const Pack<T, V> qcr = *reinterpret_cast<const Pack<T, V>*>(s_uc + (size_t)rl * K + slot);
+                if (HAS_UP) pv = ld_pack<T, V, LD_STREAM>(up + off);
+                const Pack<T, V> qcr = ld_pack<T, V, LD_READONLY>(uc + off);
                 if constexpr (REPLAY) {
                   Pack<T, V> yv = ytile[REPLAY ? ps : 0];
 #pragma unroll
