@@ -472,7 +472,7 @@ def run_side_configs(args, peak_hbm: float) -> dict:
 	from scripts import run_configs as rc
 
 	out = {}
-	a = types.SimpleNamespace(c3_scale=args.c3_scale, c3_probes=64, c3_reorder="balance", c4_n=32768, c5_grid=256, c5_small=48)
+	a = types.SimpleNamespace(c3_scale=args.c3_scale, c3_probes=64, c3_block=64, c3_reorder="balance", c4_n=32768, c5_grid=256, c5_small=48)
 
 	def guarded(name, fn):
 		t0 = time.perf_counter()
@@ -493,9 +493,9 @@ def run_side_configs(args, peak_hbm: float) -> dict:
 	def c3():
 		r = rc.c3(a)
 		n, nnz = r["n"], r["nnz"]
-		bstep = (nnz * 8 + (n + 1) * 4) / 32 + 6 * n * 4
+		bstep = (nnz * 8 + (n + 1) * 4) / r.get("block", 32) + 6 * n * 4
 		ach = bstep * r["probe_steps_per_s"] / 1e9
-		return {"workload": f"C3: tr exp(-tL), R-MAT scale {a.c3_scale} (n={n}, nnz={nnz}, max degree {r['max_degree']}), fp32, deg=30, {a.c3_probes} probes (BASELINE size: scale 24)",
+		return {"workload": f"C3: tr exp(-tL), R-MAT scale {a.c3_scale} (n={n}, nnz={nnz}, max degree {r['max_degree']}), fp32, deg=30, {a.c3_probes} probes in blocks of {a.c3_block} (BASELINE size: scale 24)",
 		        "probe_steps_per_s": r["probe_steps_per_s"], "ok": r["ok"],
 		        "roofline": {"bound": "hbm", "achieved": ach, "peak": peak_hbm, "unit": "GB/s", "frac": ach / peak_hbm,
 		                     "algorithmic_bytes_per_probe_step": bstep}}  # fmt: skip

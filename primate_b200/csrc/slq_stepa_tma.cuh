@@ -83,14 +83,19 @@ __device__ __forceinline__ void cp_async_wait() {
 // BAL: layout of the non-zero-balanced variant (irregular operators): larger index chunks, fewer stages, row sums in smem.
 template <typename T, int K, bool BAL = false>
 struct TmaTiling {
-  static constexpr int CW = 15;                        // consumer warps (+1 producer = 512 threads: 128 registers each)
+  // consumer warps (+1 producer).  Lean: 15 (512 threads, 128 registers each, one CTA per SM).  Balanced: 11 (384
+  // threads) and TWO CTAs per SM -- its consumers meet at two CTA barriers per chunk (the slice hand-over of rows that
+  // span slices), and a second, independent CTA fills the issue slots the first one leaves idle while it waits there.
+  static constexpr int CW = BAL ? 11 : 15;
+  static constexpr int CTAS_PER_SM = BAL ? 2 : 1;
   static constexpr int CT = CW * 32;                   // consumer threads
   static constexpr int NTHREADS = CT + 32;             // + producer warp
   static constexpr int V = 16 / (int)sizeof(T);        // 16-byte slices
   static constexpr int LPR = K / V;                    // lanes per row
   static constexpr int RPP = CT / LPR;                 // rows per pass
   static constexpr int TILE_MAX = 30720 / (K * (int)sizeof(T));  // staged panels of at most 30 KB each
-  static constexpr int TILE = TILE_MAX < 120 ? TILE_MAX : 120;   // rows per tile (= the cluster size of the locality ordering)
+  // rows per tile: lean = the cluster size of the locality ordering (120); balanced = 4 passes of the row groups
+  static constexpr int TILE = BAL ? 4 * RPP : (TILE_MAX < 120 ? TILE_MAX : 120);
   static constexpr int PASSES = TILE / RPP;
   static constexpr int R = PASSES % SLQ_TMA_R == 0 ? SLQ_TMA_R : 1;  // rows per thread processed together
   static constexpr size_t PANEL = (size_t)TILE * K * sizeof(T);
@@ -98,16 +103,13 @@ struct TmaTiling {
   // tile-local); the shared memory goes to a ring of RING 16-byte slots PER CONSUMER THREAD instead, filled by
   // cp.async gathers that run RING non-zeros ahead of the FMAs -- bytes in flight are bounded by shared memory
   // (RING x 480 x 16 B = 120 KB per SM), not by the 128-register budget (8 x 16 B per thread before).
-  static constexpr int RING = 16;
+  static constexpr int RING = 8;
   static constexpr size_t RING_BYTES = (size_t)RING * CT * 16;
   static constexpr size_t BAL_EXTRA = PANEL + RING_BYTES + (size_t)RPP * 4 + 32;  // row sums + gather ring + continuation rows
-  static constexpr size_t BAL_BUDGET = 216 * 1024;
-  static constexpr bool bal_fits(int cap, int stages) {
-    return (size_t)stages * ((size_t)cap * (sizeof(T) + 4) + 1024) + BAL_EXTRA <= BAL_BUDGET;
-  }
-  // balanced variant: the chunk is the unit of the per-chunk barriers and of the slice bookkeeping, so as large as fits
-  static constexpr int BAL_CAP = bal_fits(3840, 2) ? 3840 : (bal_fits(1920, 2) ? 1920 : 960);
-  static constexpr int BAL_STAGES = bal_fits(BAL_CAP, 3) ? 3 : 2;
+  static constexpr size_t BAL_BUDGET = 100 * 1024;  // two CTAs per SM
+  static constexpr int BAL_STAGES = 2;
+  // the chunk is the unit of the per-chunk barriers and of the slice bookkeeping: as large as the budget allows
+  static constexpr int BAL_CAP = (int)((((BAL_BUDGET - BAL_EXTRA) / BAL_STAGES - 1024) / (sizeof(T) + 4)) / 128 * 128);
   static constexpr int CAP = BAL ? BAL_CAP : 960;      // non-zeros per stage (lean: 8 per row; longer slices go in chunks)
   static constexpr int STAGES = SLQ_TMA_STAGES;
   static constexpr int NRP = (TILE + 1 + 31) / 32;     // row pointers per producer lane
@@ -125,7 +127,7 @@ struct TmaTiling {
   static constexpr size_t STAGE_BYTES = (OFF_HDR + 16 + 4 * MAXLONG + 127) / 128 * 128;  // header: lo, hi, last, nlong, long rows
   static constexpr size_t SMEM_BYTES = STAGE_BYTES * STAGES;
   static constexpr size_t SMEM_BAL = STAGE_BYTES * BAL_STAGES + BAL_EXTRA;
-  static_assert(!BAL || SMEM_BAL <= 216 * 1024, "balanced variant does not fit in shared memory");
+  static_assert(!BAL || (SMEM_BAL <= 101 * 1024 && BAL_CAP >= 512), "balanced variant does not fit in shared memory");
   static_assert(K % V == 0 && LPR >= 4 && LPR <= 32, "block width not supported by the TMA kernel");
   static_assert(PASSES >= 1 && PASSES * RPP == TILE, "tile must be a whole number of passes");
 };
@@ -192,7 +194,7 @@ __device__ __forceinline__ void tma_gather_rows(T (&acc)[R][V], const int (&s)[R
 // LONGROWS = false: compiled without the shared long-row path (operators whose longest row has <= LONG non-zeros; the
 // extra live state costs the lean kernel registers -- it spilled and ran 2.4x slower with the path compiled in).
 template <typename T, int K, int MODE, bool LONGROWS>
-__global__ void __launch_bounds__(TmaTiling<T, K, LONGROWS>::NTHREADS, 1)
+__global__ void __launch_bounds__(TmaTiling<T, K, LONGROWS>::NTHREADS, TmaTiling<T, K, LONGROWS>::CTAS_PER_SM)
     k_stepA_tma(int n, const int32_t* __restrict__ rowptr, const int32_t* __restrict__ colidx, const T* __restrict__ vals,
                 const T* __restrict__ uc, const T* __restrict__ up, T* __restrict__ w, LzScal* sc, const double* scale_c,
                 const double* scale_p, double* partial, StepOut so, ReplayArgs rp) {
@@ -698,8 +700,10 @@ static int launch_stepA_tma(const slq_op* op, const T* uc, const T* up, T* w, Lz
   const int n = (int)op->n;
   const int ntiles = (n + C::TILE - 1) / C::TILE;
   const int g = ntiles < sm_count() ? ntiles : sm_count();
+  const int ntiles_b = (n + CB::TILE - 1) / CB::TILE;
+  const int gb = ntiles_b < CB::CTAS_PER_SM * sm_count() ? ntiles_b : CB::CTAS_PER_SM * sm_count();
   if (op->max_row_nnz > C::LONG)
-    k_stepA_tma<T, K, MODE, true><<<g, C::NTHREADS, CB::SMEM_BAL, st>>>(n, op->rowptr, op->colidx, (const T*)op->vals, uc, up, w, sc,
+    k_stepA_tma<T, K, MODE, true><<<gb, CB::NTHREADS, CB::SMEM_BAL, st>>>(n, op->rowptr, op->colidx, (const T*)op->vals, uc, up, w, sc,
                                                                          scale_c, scale_p, partial, so, rp);
   else
     k_stepA_tma<T, K, MODE, false><<<g, C::NTHREADS, C::SMEM_BYTES, st>>>(n, op->rowptr, op->colidx, (const T*)op->vals, uc, up, w, sc,
