@@ -509,6 +509,16 @@ def quadrature(alpha, beta, deg: int, fun_id: int = -1, params=None, scale=None,
 	return theta, tau, y, info
 
 
+def warn_unconverged(info, where: str) -> None:
+	"""Host-facing solvers (which synchronise anyway) report eigenvalues that ran out of QL sweeps; the reference's tqli
+	tolerates the same silently (tqli.py:54-56), its LAPACK path would raise and fall back (tridiag.py:16-20)."""
+	bad = int((info > 0).sum().item())
+	if bad:
+		import warnings
+
+		warnings.warn(f"{where}: {bad} Jacobi matrices had eigenvalues that did not converge within the QL sweep limit", RuntimeWarning, stacklevel=3)
+
+
 def funm_coeffs(alpha, beta, deg: int, fun_id: int, params=None):
 	"""Krylov coefficients c_p = Y f(Theta) Y^T e_1 (k, deg) plus (theta, tau)."""
 	torch = _torch()

@@ -32,7 +32,8 @@ def quadrature(
 		dt = np.float32 if d.dtype == np.float32 else np.float64
 		a = torch.from_numpy(np.ascontiguousarray(d[:deg], dtype=dt)[None, :].copy()).cuda()
 		b = torch.from_numpy(np.ascontiguousarray(e[:deg], dtype=dt)[None, :].copy()).cuda()
-		th, ta, _, _ = engine.quadrature(a, b, deg, fun_id=-1)
+		th, ta, _, info = engine.quadrature(a, b, deg, fun_id=-1)
+		engine.warn_unconverged(info, "quadrature")
 		theta, tau = th.cpu().numpy()[0].astype(d.dtype, copy=False), ta.cpu().numpy()[0].astype(d.dtype, copy=False)
 	elif quad == "fttr":
 		theta = eigvalsh_tridiag(d, e, **kwargs)

@@ -26,8 +26,10 @@ def _device_eigh(d: np.ndarray, e: np.ndarray, vectors: bool):
 	b = torch.from_numpy(e[None, :].copy()).cuda()
 	if not vectors:
 		theta, _, _, info = engine.quadrature(a, b, m, fun_id=-1)
+		engine.warn_unconverged(info, "eigvalsh_tridiag")
 		return theta.cpu().numpy()[0].astype(d.dtype)
 	_, theta, _, scratch, info = engine.funm_coeffs(a, b, m, fun_id=-1)
+	engine.warn_unconverged(info, "eigh_tridiag")
 	scratch = scratch.cpu().numpy()
 	Zt = scratch[: m * m].reshape(m, m)  # Zt[col, row]
 	perm = scratch[m * m :].astype(np.int64)
