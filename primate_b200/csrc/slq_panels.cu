@@ -9,10 +9,17 @@
 // Panels are row-major with a row stride (ld), so column ranges of a wider buffer are panels too.  All reductions are
 // deterministic (per-CTA partial tables summed in a fixed order), accumulate in fp64 and return fp64.
 #include <algorithm>
+#include <cstdlib>
+#include <cstring>
+#include <type_traits>
 
 #include "slq_internal.cuh"
 
 namespace slq {
+
+__device__ __forceinline__ void panel_dmma(double (&c)[2], double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c[0]), "+d"(c[1]) : "d"(a), "d"(b));
+}
 
 constexpr int PG_T = 16;   // thread grid 16 x 16
 constexpr int PG_TILE = 128;  // output tile (rows of G x columns of G) per CTA: 8 x 8 per thread
@@ -70,6 +77,63 @@ __global__ void __launch_bounds__(256) k_panel_gram(const T* __restrict__ X, int
       const int ii = ty + PG_T * i, jj = tx + PG_T * j;
       if (ii < ta && jj < tb) out[ii * PG_TILE + jj] = acc[i][j];
     }
+}
+
+// fp64 tensor-core variant of the Gram-type reduction (a % 8 == 0, b % 8 == 0, a, b <= 96): G = X^T Y is an (a x b)
+// sum of rank-4 updates, one DMMA m8n8k4 per 8 x 8 output tile and 4 panel rows.  The 8 warps of a CTA form a
+// WI x WJ grid over the output tiles times a WR-way split of the rows; the A / B fragments (4 rows x 8 columns of X / Y,
+// one double per lane, 64-byte row segments) come straight from global memory.  Every (CTA, row split) pair writes
+// its partial tiles to the partial table; the reduce kernel sums them in a fixed order.
+template <int TI, int TJ, int WI, int WJ>
+__global__ void __launch_bounds__(256) k_panel_gram_dmma(const double* __restrict__ X, int a, int64_t ldx, const double* __restrict__ Y,
+                                                          int b, int64_t ldy, int64_t row0, int64_t row1, double* __restrict__ partial) {
+  constexpr int WR = 8 / (WI * WJ);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int g = lane >> 2, t = lane & 3;
+  const int wi = warp % WI, wj = (warp / WI) % WJ, wr = warp / (WI * WJ);
+  const int ib0 = wi * TI, jb0 = wj * TJ;  // first 8-blocks of this warp's output rectangle
+  double acc[TI][TJ][2];
+#pragma unroll
+  for (int i = 0; i < TI; ++i)
+#pragma unroll
+    for (int j = 0; j < TJ; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+  // rows in groups of 4; group index q = (CTA-strided chunk) interleaved over the WR row splits
+  const int64_t groups = (row1 - row0 + 3) / 4;
+  for (int64_t q = (int64_t)blockIdx.x * WR + wr; q < groups; q += (int64_t)gridDim.x * WR) {
+    const int64_t r = row0 + q * 4 + t;
+    const bool ok = r < row1;
+    const double* xr = X + (ok ? r : row0) * ldx + g;
+    const double* yr = Y + (ok ? r : row0) * ldy + g;
+    double av[TI], bv[TJ];
+#pragma unroll
+    for (int i = 0; i < TI; ++i) av[i] = (ok && (ib0 + i) * 8 < a) ? __ldg(xr + (ib0 + i) * 8) : 0.0;
+#pragma unroll
+    for (int j = 0; j < TJ; ++j) bv[j] = (ok && (jb0 + j) * 8 < b) ? __ldg(yr + (jb0 + j) * 8) : 0.0;
+#pragma unroll
+    for (int i = 0; i < TI; ++i)
+#pragma unroll
+      for (int j = 0; j < TJ; ++j) panel_dmma(acc[i][j], av[i], bv[j]);
+  }
+  // partial table entry of (CTA, row split): an a x b row-major matrix
+  double* out = partial + ((size_t)blockIdx.x * WR + wr) * ((size_t)a * b);
+#pragma unroll
+  for (int i = 0; i < TI; ++i)
+#pragma unroll
+    for (int j = 0; j < TJ; ++j) {
+      const int gi = (ib0 + i) * 8 + g, gj = (jb0 + j) * 8 + 2 * t;
+      if (gi < a && gj < b) {
+        out[(size_t)gi * b + gj] = acc[i][j][0];
+        out[(size_t)gi * b + gj + 1] = acc[i][j][1];
+      }
+    }
+}
+
+__global__ void k_panel_gram_reduce_flat(const double* __restrict__ partial, int nparts, int ab, double* __restrict__ G) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= ab) return;
+  double s = 0.0;
+  for (int p = 0; p < nparts; ++p) s += partial[(size_t)p * ab + idx];
+  G[idx] = s;
 }
 
 __global__ void k_panel_gram_reduce(const double* __restrict__ partial, int nparts, int a, int b, double* __restrict__ G) {
@@ -144,6 +208,85 @@ __global__ void __launch_bounds__(256) k_panel_matmul(const T* __restrict__ X, i
   }
 }
 
+// fp64 tensor-core variant of the panel product (a % 4 == 0, b % 8 == 0, b <= 96 per grid.y tile): every warp owns 16
+// rows of Y; the A fragments (8 rows x 4 columns of X: one double per lane, 32-byte row segments) come straight from
+// global memory -- each sector of X is read exactly once over the k loop -- the B fragments from S staged in shared
+// memory (row stride = 4 (mod 16) doubles: conflict-free), the product accumulates in DMMA m8n8k4 tiles.  The panel
+// passes of the block drivers are then HBM-bound (read X, write Y) instead of FMA-issue-bound (measured 2 TFLOP/s with
+// the scalar kernel at m = 32: 17 ms per pass at n = 16.7 M against 1.4 ms of memory time).
+constexpr int PD_BT = 96;
+template <int NB>  // 8-column blocks of this tile
+__global__ void __launch_bounds__(256) k_panel_matmul_dmma(const double* __restrict__ X, int a, int64_t ldx, const double* __restrict__ S,
+                                                            int b, double alpha, double beta, double* __restrict__ Y, int64_t ldy,
+                                                            int64_t n) {
+  extern __shared__ double sS[];  // a x (8 NB + 4)
+  constexpr int BP = 8 * NB + 4;
+  const int j0 = blockIdx.y * PD_BT;
+  for (int idx = threadIdx.x; idx < a * 8 * NB; idx += 256) {
+    const int kk = idx / (8 * NB), j = idx % (8 * NB);
+    sS[kk * BP + j] = (j0 + j < b) ? S[(size_t)kk * b + j0 + j] : 0.0;
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int g = lane >> 2, t = lane & 3;
+  const int64_t slabs = (n + 15) / 16;
+  for (int64_t sl = (int64_t)blockIdx.x * 8 + warp; sl < slabs; sl += (int64_t)gridDim.x * 8) {
+    const int64_t r0 = sl * 16;
+    double acc[2][NB][2];
+#pragma unroll
+    for (int mb = 0; mb < 2; ++mb)
+#pragma unroll
+      for (int nb = 0; nb < NB; ++nb) acc[mb][nb][0] = acc[mb][nb][1] = 0.0;
+    const int64_t ra = r0 + g, rb = r0 + 8 + g;
+    const double* xa = X + (ra < n ? ra : n - 1) * ldx + t;  // rows past the end read the last row (never stored)
+    const double* xb = X + (rb < n ? rb : n - 1) * ldx + t;
+#pragma unroll 4
+    for (int k0 = 0; k0 < a; k0 += 4) {
+      const double a0 = __ldg(xa + k0), a1 = __ldg(xb + k0);
+#pragma unroll
+      for (int nb = 0; nb < NB; ++nb) {
+        const double bv = sS[(k0 + t) * BP + nb * 8 + g];
+        panel_dmma(acc[0][nb], a0, bv);
+        panel_dmma(acc[1][nb], a1, bv);
+      }
+    }
+#pragma unroll
+    for (int mb = 0; mb < 2; ++mb) {
+      const int64_t r = r0 + mb * 8 + g;
+      if (r < n) {
+#pragma unroll
+        for (int nb = 0; nb < NB; ++nb) {
+          const int j = j0 + nb * 8 + 2 * t;
+          if (j < b) {  // b % 8 == 0: the pair (j, j + 1) is inside or outside together
+            double* y = Y + r * ldy + j;
+            double o0 = alpha * acc[mb][nb][0], o1 = alpha * acc[mb][nb][1];
+            if (beta != 0.0) {
+              o0 += beta * y[0];
+              o1 += beta * y[1];
+            }
+            y[0] = o0;
+            y[1] = o1;
+          }
+        }
+      }
+    }
+  }
+}
+
+template <int NB>
+static int launch_panel_matmul_dmma(const double* X, int a, int64_t ldx, const double* S, int b, double alpha, double beta, double* Y,
+                                    int64_t ldy, int64_t n, dim3 grid, cudaStream_t st) {
+  const size_t smem = sizeof(double) * (size_t)a * (8 * NB + 4);
+  static DeviceOnce once;
+  if (smem > 48 * 1024 && once.needed()) {
+    SLQ_CUDA(cudaFuncSetAttribute(k_panel_matmul_dmma<NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    once.done();
+  }
+  k_panel_matmul_dmma<NB><<<grid, 256, smem, st>>>(X, a, ldx, S, b, alpha, beta, Y, ldy, n);
+  SLQ_LAUNCH_CHECK();
+  return SLQ_OK;
+}
+
 // out[r] = sum_j X[r][j] * Y[r][j]   (one warp per row)
 template <typename T>
 __global__ void __launch_bounds__(256) k_panel_rowdot(const T* __restrict__ X, int64_t ldx, const T* __restrict__ Y, int64_t ldy, int m,
@@ -210,7 +353,9 @@ size_t slq_panel_gram_workspace_bytes(int a, int b) {
   if (a <= 0 || b <= 0) return 0;
   const int sms = sm_count() > 0 ? sm_count() : 148;
   const size_t tiles = (size_t)((a + PG_TILE - 1) / PG_TILE) * ((b + PG_TILE - 1) / PG_TILE);
-  return align_up(sizeof(double) * 2 * (size_t)sms * tiles * PG_TILE * PG_TILE, 256);
+  const size_t fma = sizeof(double) * 2 * (size_t)sms * tiles * PG_TILE * PG_TILE;
+  const size_t dmma = sizeof(double) * 2 * (size_t)sms * 8 * (size_t)a * b;  // (CTA, row split) partials of the tensor-core variant
+  return align_up(fma > dmma ? fma : dmma, 256);
 }
 
 int slq_panel_gram(const void* X_dev, int a, int64_t ldx, const void* Y_dev, int b, int64_t ldy, int64_t row0, int64_t row1, int dtype,
@@ -225,10 +370,30 @@ int slq_panel_gram(const void* X_dev, int a, int64_t ldx, const void* Y_dev, int
     SLQ_CUDA(cudaMemsetAsync(G_dev, 0, sizeof(double) * (size_t)a * b, st));
     return SLQ_OK;
   }
+  double* partial = (double*)workspace_dev;
+  static const bool fma_only = [] { const char* e = getenv("SLQ_PANEL"); return e && strcmp(e, "fma") == 0; }();
+  if (dtype == SLQ_F64 && !fma_only && a % 8 == 0 && b % 8 == 0 && a <= 96 && b <= 96) {
+    const int sms = sm_count();
+    const int64_t groups = (row1 - row0 + 3) / 4;
+    const int mx = a > b ? a : b;
+    const int wr = mx <= 32 ? 8 : (mx <= 64 ? 4 : 2);  // row splits per CTA (see the warp grids below)
+    const int gx = (int)std::max<int64_t>(1, std::min<int64_t>((groups + wr * 64 - 1) / (wr * 64), 2 * (int64_t)sms));
+    const double* Xd = (const double*)X_dev;
+    const double* Yd = (const double*)Y_dev;
+    if (mx <= 32)
+      k_panel_gram_dmma<4, 4, 1, 1><<<gx, 256, 0, st>>>(Xd, a, ldx, Yd, b, ldy, row0, row1, partial);
+    else if (mx <= 64)
+      k_panel_gram_dmma<4, 8, 2, 1><<<gx, 256, 0, st>>>(Xd, a, ldx, Yd, b, ldy, row0, row1, partial);
+    else
+      k_panel_gram_dmma<6, 6, 2, 2><<<gx, 256, 0, st>>>(Xd, a, ldx, Yd, b, ldy, row0, row1, partial);
+    SLQ_LAUNCH_CHECK();
+    k_panel_gram_reduce_flat<<<(a * b + 255) / 256, 256, 0, st>>>(partial, gx * wr, a * b, G_dev);
+    SLQ_LAUNCH_CHECK();
+    return SLQ_OK;
+  }
   const int tiles = ((a + PG_TILE - 1) / PG_TILE) * ((b + PG_TILE - 1) / PG_TILE);
   const int gx = gram_grid(row1 - row0);
   dim3 grid((unsigned)gx, (unsigned)tiles);
-  double* partial = (double*)workspace_dev;
   if (dtype == SLQ_F64)
     k_panel_gram<double><<<grid, 256, 0, st>>>((const double*)X_dev, a, ldx, (const double*)Y_dev, b, ldy, row0, row1, partial);
   else
@@ -250,6 +415,43 @@ int slq_panel_matmul(const void* X_dev, int a, int64_t ldx, const double* S_dev,
   const int64_t chunks = (n + PM_RC - 1) / PM_RC;
   dim3 grid((unsigned)std::min<int64_t>(chunks, 4 * (int64_t)sms), (unsigned)((b + PM_BT - 1) / PM_BT));
   cudaStream_t st = (cudaStream_t)stream;
+  static const bool fma_only = [] { const char* e = getenv("SLQ_PANEL"); return e && strcmp(e, "fma") == 0; }();
+  if (dtype == SLQ_F64 && !fma_only && a % 4 == 0 && b % 8 == 0 && (size_t)a * (PD_BT + 4) * sizeof(double) <= 200 * 1024) {
+    // fp64 tensor-core tiles: column tiles of at most 96, 16-row slabs per warp
+    const int tiles = (b + PD_BT - 1) / PD_BT;
+    const int64_t slabs = (n + 15) / 16;
+    dim3 gd((unsigned)std::max<int64_t>(1, std::min<int64_t>((slabs + 7) / 8, 8 * (int64_t)sms)), (unsigned)tiles);
+    const double* Xd = (const double*)X_dev;
+    double* Yd = (double*)Y_dev;
+    const int nb_last = ((b - (tiles - 1) * PD_BT) + 7) / 8;  // 8-column blocks in the last (or only) tile
+    if (tiles > 1) {  // full tiles first, then the remainder tile with its own width
+      dim3 gfull(gd.x, (unsigned)(tiles - 1));
+      int rc = launch_panel_matmul_dmma<12>(Xd, a, ldx, S_dev, b, alpha, beta, Yd, ldy, n, gfull, st);
+      if (rc != SLQ_OK) return rc;
+    }
+    // the remainder tile starts at column (tiles - 1) * 96: shift the pointers, keep S's row stride via the b argument
+    const int joff = (tiles - 1) * PD_BT;
+    dim3 g1(gd.x, 1);
+    auto go = [&](auto tag) {
+      constexpr int NBv = decltype(tag)::value;
+      // blockIdx.y == 0 in this launch, so the column offset is applied by hand
+      return launch_panel_matmul_dmma<NBv>(Xd, a, ldx, S_dev + joff, b, alpha, beta, Yd + joff, ldy, n, g1, st);
+    };
+    switch (nb_last) {
+      case 1: return go(std::integral_constant<int, 1>{});
+      case 2: return go(std::integral_constant<int, 2>{});
+      case 3: return go(std::integral_constant<int, 3>{});
+      case 4: return go(std::integral_constant<int, 4>{});
+      case 5: return go(std::integral_constant<int, 5>{});
+      case 6: return go(std::integral_constant<int, 6>{});
+      case 7: return go(std::integral_constant<int, 7>{});
+      case 8: return go(std::integral_constant<int, 8>{});
+      case 9: return go(std::integral_constant<int, 9>{});
+      case 10: return go(std::integral_constant<int, 10>{});
+      case 11: return go(std::integral_constant<int, 11>{});
+      default: return go(std::integral_constant<int, 12>{});
+    }
+  }
   if (dtype == SLQ_F64)
     k_panel_matmul<double><<<grid, 256, 0, st>>>((const double*)X_dev, a, ldx, S_dev, b, alpha, beta, (double*)Y_dev, ldy, n);
   else

@@ -23,7 +23,8 @@ def P():
 	return make
 
 
-@pytest.mark.parametrize("n,a,b", [(1000, 7, 7), (5003, 37, 96), (2048, 130, 200), (333, 1, 64), (40000, 96, 96)])
+@pytest.mark.parametrize("n,a,b", [(1000, 7, 7), (5003, 37, 96), (2048, 130, 200), (333, 1, 64), (40000, 96, 96), (3001, 32, 32), (7001, 64, 200),
+                                   (515, 96, 104), (17, 4, 8)])
 @pytest.mark.parametrize("dtype", [np.float64, np.float32])
 def test_gram_matmul_dots_vs_numpy(P, n, a, b, dtype):
 	import torch
