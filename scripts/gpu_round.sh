@@ -17,7 +17,7 @@ cat $OUT/bench.json
 echo "== bench --impl reference"
 timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > $OUT/bench_ref.json 2> $OUT/bench_ref.err; echo "ref exit $?"
 cat $OUT/bench_ref.json
-SMALL="python bench.py --steps 1 --warmup 3 --probes 64 --no-cpu-baseline --no-e2e"
+SMALL="python bench.py --steps 1 --warmup 3 --probes 64 --no-cpu-baseline --no-e2e --no-configs"
 echo "== ncu launch list"
 $SMALL > $OUT/plain_small.log 2>&1 &&
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -s 330 -c 112 --csv --log-file $OUT/launches.csv $SMALL > $OUT/ncu_launches.log 2>&1
