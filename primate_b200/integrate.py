@@ -75,13 +75,12 @@ def spectral_density(
 	stream.finish(int(count))
 	theta, tau = theta.cpu().numpy(), tau.cpu().numpy()
 	lo, hi = float(theta.min()), float(theta.max())
-	if np.isscalar(points):
-		pad = 0.02 * (hi - lo if hi > lo else 1.0)
-		t = np.linspace(lo - pad, hi + pad, int(points))
-	else:
-		t = np.asarray(points, dtype=np.float64)
 	if sigma is None:
 		sigma = 2.0 * (hi - lo if hi > lo else 1.0) / theta.shape[1]
+	if np.isscalar(points):
+		t = np.linspace(lo - 5.0 * sigma, hi + 5.0 * sigma, int(points))  # the smoothed measure keeps its unit mass on the grid
+	else:
+		t = np.asarray(points, dtype=np.float64)
 	z = (t[:, None] - theta.reshape(1, -1)) / sigma
 	dens = (np.exp(-0.5 * z * z) * tau.reshape(1, -1)).sum(axis=1) / (np.sqrt(2 * np.pi) * sigma * theta.shape[0])
 	return (t, dens, theta, tau) if full else (t, dens)
