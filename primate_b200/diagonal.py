@@ -64,7 +64,9 @@ def xdiag(A: np.ndarray, m: Optional[int] = None, pdf: str = "sphere", seed: Uni
 	finish(m)
 	Y = P.product(Nw)
 	Q, R = P.qr(Y)
-	dNY = P.rowdot(Nw, Y)
+	lo, hi = P.row_slice()  # with one process per GPU: this rank's rows of the row-local part below
+	Nr = P.rows(Nw, lo, hi)
+	dNY = P.rowdot(Nr, P.rows(Y, lo, hi))
 	del Y
 	Z = P.product(Q) if P.on_device else A.T @ Q
 
@@ -74,10 +76,11 @@ def xdiag(A: np.ndarray, m: Optional[int] = None, pdf: str = "sphere", seed: Uni
 	S = R_inv.T / np.linalg.norm(R_inv, axis=1)
 	dST = np.einsum("ij,ij->j", S, T)
 
-	## diagonals of the n x n products, one row-dot of two panels each
-	dQZ = P.rowdot(Q, Z)
-	dQSSZ = P.rowdot(P.matmul(Q, S), P.matmul(Z, S))
-	dNTQ = P.rowdot(Nw, P.matmul(Q, T))
-	dNQSST = P.rowdot(Nw, P.matmul(Q, S * dST[np.newaxis, :]))
+	## diagonals of the n x n products, one row-dot of two panels each: row-local, so every rank does its slice
+	Qr, Zr = P.rows(Q, lo, hi), P.rows(Z, lo, hi)
+	dQZ = P.rowdot(Qr, Zr)
+	dQSSZ = P.rowdot(P.matmul(Qr, S), P.matmul(Zr, S))
+	dNTQ = P.rowdot(Nr, P.matmul(Qr, T))
+	dNQSST = P.rowdot(Nr, P.matmul(Qr, S * dST[np.newaxis, :]))
 	d = dQZ + (-dQSSZ + dNY - dNTQ + dNQSST) / m
-	return np.ravel(P.to_host(d))
+	return np.ravel(P.to_host(P.gather_rows(d)))

@@ -96,6 +96,15 @@ class HostPanels:
 	def to_host(self, v):
 		return np.asarray(v, dtype=np.float64)
 
+	def row_slice(self):
+		return 0, self.n
+
+	def rows(self, X, lo: int, hi: int):
+		return X[lo:hi]
+
+	def gather_rows(self, v_local):
+		return v_local
+
 
 class DevicePanels:
 	"""libslq backend for a `MatrixFunction` M and a device `ProbeStream`."""
@@ -170,10 +179,11 @@ class DevicePanels:
 		a, b = S.shape
 		assert int(X.shape[1]) == a
 		Sd = self.torch.from_numpy(S).cuda()
+		rows = int(X.shape[0])  # the full panel, or a rank's row slice of it
 		if out is None:
-			out = self.torch.empty((self.n, b), dtype=X.dtype, device="cuda")
+			out = self.torch.empty((rows, b), dtype=X.dtype, device="cuda")
 		self._ffi.check(L.slq_panel_matmul(X.data_ptr(), a, self._ld(X), Sd.data_ptr(), b, float(alpha), float(beta), out.data_ptr(),
-		                                   self._ld(out), self.n, self.code, self._engine._stream_ptr()))  # fmt: skip
+		                                   self._ld(out), rows, self.code, self._engine._stream_ptr()))  # fmt: skip
 		return out
 
 	def matmul(self, X, S):
@@ -184,8 +194,9 @@ class DevicePanels:
 
 	def rowdot(self, X, Y):
 		L = self._ffi.lib()
-		out = self.torch.empty(self.n, dtype=self.torch.float64, device="cuda")
-		self._ffi.check(L.slq_panel_rowdot(X.data_ptr(), self._ld(X), Y.data_ptr(), self._ld(Y), int(X.shape[1]), self.n, self.code,
+		rows = int(X.shape[0])
+		out = self.torch.empty(rows, dtype=self.torch.float64, device="cuda")
+		self._ffi.check(L.slq_panel_rowdot(X.data_ptr(), self._ld(X), Y.data_ptr(), self._ld(Y), int(X.shape[1]), rows, self.code,
 		                                   out.data_ptr(), self._engine._stream_ptr()))  # fmt: skip
 		return out
 
@@ -222,6 +233,23 @@ class DevicePanels:
 
 	def to_host(self, v):
 		return v.double().cpu().numpy() if hasattr(v, "cpu") else np.asarray(v, dtype=np.float64)
+
+	def row_slice(self):
+		"""Rows whose entries of an n-vector result this rank computes (all of them without a comm): everything after the
+		thin QR in XDiag is row-local, so the replicated panels are only ever multiplied on a 1/ranks slice of their rows."""
+		return self._rows()
+
+	def rows(self, X, lo: int, hi: int):
+		return X[lo:hi]
+
+	def gather_rows(self, v_local):
+		"""Concatenates the ranks' row slices of an n-vector (one all-gather of n doubles)."""
+		if self.comm is None:
+			return v_local
+		per = -(-self.n // self.comm.size)
+		pad = self.torch.zeros(per, dtype=self.torch.float64, device="cuda")
+		pad[: v_local.numel()] = v_local
+		return self.comm.all_gather_tensor(pad).reshape(-1)[: self.n]
 
 
 def block_orthogonalize(P, Q: Optional[object], Ynew):
