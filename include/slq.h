@@ -93,6 +93,14 @@ int slq_csr_create_ex(int64_t n, int64_t nnz, const int32_t* rowptr_dev, const i
                       const void* vals_dev, int dtype, int64_t max_row_nnz, slq_stream stream, slq_op** out);
 /* Dense symmetric n x n, leading dimension ld (row- or column-major is the same for a symmetric matrix). */
 int slq_dense_create(int64_t n, const void* A_dev, int64_t ld, int dtype, slq_op** out);
+/* As slq_dense_create for an operator whose order is not a multiple of 16: A_dev is an npad x ld array (npad = n rounded
+ * up to 16, ld >= npad) whose rows and columns >= n are ZERO.  Panels keep n rows.  The padding lets every n take the
+ * bulk-copy / tensor-core dense kernels (whole 16-byte units) instead of the generic fallback. */
+int slq_dense_create_padded(int64_t n, int64_t npad, const void* A_dev, int64_t ld, int dtype, slq_op** out);
+/* Optional caller-owned scratch for an operator (must outlive it; NULL detaches).  Small dense operators use it to split
+ * the reduction dimension of Y = A X over several CTAs per row tile (partial slabs of n x k, summed in a fixed order):
+ * 16 n k sizeof(T) bytes allow the full split.  Calls that use the scratch must not overlap on different streams. */
+int slq_op_set_scratch(slq_op* op, void* scratch_dev, size_t bytes);
 /* Matrix-free operator driven by a callback (device panels in, device panels out). */
 int slq_callback_create(int64_t n, int dtype, slq_matmat_fn fn, void* ctx, slq_op** out);
 int slq_op_destroy(slq_op* op);

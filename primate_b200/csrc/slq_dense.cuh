@@ -44,7 +44,7 @@ constexpr bool dense_tma_supported() {
 // SMs (n = 32 768 on 148 SMs at two CTAs per SM: 293 tiles of 112 rows, at most 224 rows per SM instead of 256).
 template <typename T, int K, int RPT>
 __global__ void __launch_bounds__(DenseTiling<T, K, RPT>::NTD, 2)
-    k_dense_tma(int n, const T* __restrict__ A, int64_t ld, const T* __restrict__ X, T* __restrict__ Y) {
+    k_dense_tma(int n, int npad, const T* __restrict__ A, int64_t ld, const T* __restrict__ X, T* __restrict__ Y) {
   using D = DenseTiling<T, K, RPT>;
   constexpr int TR = D::TR, KC = D::KC, STAGES = D::STAGES, CW = D::CW;
   constexpr int CP = CW >= 2 ? CW / 2 : 1;  // column pairs (or the single column) per thread
@@ -54,7 +54,9 @@ __global__ void __launch_bounds__(DenseTiling<T, K, RPT>::NTD, 2)
   __shared__ uint64_t bar_full[STAGES], bar_empty[STAGES];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int row0 = blockIdx.x * TR;
-  const int rows = min(TR, n - row0);  // the last tile may be short (n is a multiple of 16: whole 16-byte units)
+  // A is npad x npad (npad = n rounded up to 16, rows / columns >= n zero: slq_dense_create_padded), the panels have n
+  // rows: tiles and chunks are whole 16-byte units of the padded operator, the last X slab is short, stores stop at n.
+  const int rows = min(TR, npad - row0);
   if (tid == 0) {
 #pragma unroll
     for (int s = 0; s < STAGES; ++s) {
@@ -63,18 +65,31 @@ __global__ void __launch_bounds__(DenseTiling<T, K, RPT>::NTD, 2)
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
+  if (npad != n) {  // rows of the last X slab past n are never copied: make sure they hold zeros, not stale bits
+    for (int s = 0; s < STAGES; ++s) {
+      T* Xz = reinterpret_cast<T*>(smem_raw + (size_t)s * D::STAGE_BYTES + D::A_BYTES);
+      for (int i = tid; i < KC * K; i += D::NTD) Xz[i] = (T)0;
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy zeros before async-proxy (bulk copy) writes
+  }
   __syncthreads();
-  const int nchunks = n / KC;
+  // split-K: blockIdx.y owns the chunk range [c0, c0 + nchunks) and writes its partial product to slab blockIdx.y of Y
+  const int per_split = (npad / KC + gridDim.y - 1) / gridDim.y;
+  const int c0 = blockIdx.y * per_split;
+  const int nchunks = max(0, min(npad / KC, c0 + per_split) - c0);
+  Y += (size_t)blockIdx.y * (size_t)n * K;
   if (warp == D::NCONS / 32) {  // ---- producer warp
     const uint32_t a_line = (uint32_t)(rows * sizeof(T));
-    for (int c = 0; c < nchunks; ++c) {
-      const int s = c % STAGES;
-      if (c >= STAGES) mbar_wait(&bar_empty[s], (uint32_t)(((c / STAGES) - 1) & 1));
+    for (int ci = 0; ci < nchunks; ++ci) {
+      const int c = c0 + ci;
+      const int s = ci % STAGES;
+      if (ci >= STAGES) mbar_wait(&bar_empty[s], (uint32_t)(((ci / STAGES) - 1) & 1));
       unsigned char* S = smem_raw + (size_t)s * D::STAGE_BYTES;
-      if (lane == 0) mbar_arrive_expect_tx(&bar_full[s], (uint32_t)(KC * a_line + D::X_BYTES));
+      const uint32_t x_bytes = (uint32_t)(min(KC, n - c * KC) * K * sizeof(T));
+      if (lane == 0) mbar_arrive_expect_tx(&bar_full[s], (uint32_t)(KC * a_line + x_bytes));
       __syncwarp();
       if (lane < KC) bulk_g2s(S + (size_t)lane * TR * sizeof(T), A + (size_t)(c * KC + lane) * ld + row0, a_line, &bar_full[s]);
-      if (lane == KC) bulk_g2s(S + D::A_BYTES, X + (size_t)c * KC * K, (uint32_t)D::X_BYTES, &bar_full[s]);
+      if (lane == KC) bulk_g2s(S + D::A_BYTES, X + (size_t)c * KC * K, x_bytes, &bar_full[s]);
     }
     return;
   }
@@ -88,9 +103,9 @@ __global__ void __launch_bounds__(DenseTiling<T, K, RPT>::NTD, 2)
 #pragma unroll
       for (int v = 0; v < CV; ++v) acc[i][p][v] = (T)0;
 
-  for (int c = 0; c < nchunks; ++c) {
-    const int s = c % STAGES;
-    mbar_wait(&bar_full[s], (uint32_t)((c / STAGES) & 1));
+  for (int ci = 0; ci < nchunks; ++ci) {
+    const int s = ci % STAGES;
+    mbar_wait(&bar_full[s], (uint32_t)((ci / STAGES) & 1));
     const T* As = reinterpret_cast<const T*>(smem_raw + (size_t)s * D::STAGE_BYTES);
     const T* Xs = reinterpret_cast<const T*>(smem_raw + (size_t)s * D::STAGE_BYTES + D::A_BYTES);
 #pragma unroll
@@ -119,7 +134,7 @@ __global__ void __launch_bounds__(DenseTiling<T, K, RPT>::NTD, 2)
 #pragma unroll
   for (int i = 0; i < RPT; ++i) {
     const int rl = (i < 2 * NP) ? (i / 2) * 32 + ty * 2 + (i & 1) : NP * 32 + ty;
-    if (rl < rows) {
+    if (row0 + rl < n) {
       const int r = row0 + rl;
 #pragma unroll
       for (int p = 0; p < CP; ++p) {
@@ -167,14 +182,14 @@ __device__ __forceinline__ void dmma_884(double (&c)[2], double a, double b) {
 
 template <int K, int RPT>
 __global__ void __launch_bounds__(DmmaTiling<K, RPT>::NTD, DmmaTiling<K, RPT>::CTAS)
-    k_dense_dmma(int n, const double* __restrict__ A, int64_t ld, const double* __restrict__ X, double* __restrict__ Y) {
+    k_dense_dmma(int n, int npad, const double* __restrict__ A, int64_t ld, const double* __restrict__ X, double* __restrict__ Y) {
   using D = DmmaTiling<K, RPT>;
   constexpr int TR = D::TR, KC = D::KC, STAGES = D::STAGES, NB = D::NB, TRP = D::TRP, KP = D::KP;
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ uint64_t bar_full[STAGES], bar_empty[STAGES];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int row0 = blockIdx.x * TR;
-  const int rows = min(TR, n - row0);  // n is a multiple of 16: whole 16-row warp slabs, whole 16-byte units
+  const int rows = min(TR, npad - row0);  // npad is a multiple of 16: whole 16-row warp slabs, whole 16-byte units
   if (tid == 0) {
 #pragma unroll
     for (int s = 0; s < STAGES; ++s) {
@@ -183,20 +198,33 @@ __global__ void __launch_bounds__(DmmaTiling<K, RPT>::NTD, DmmaTiling<K, RPT>::C
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
+  if (npad != n) {  // X rows past n are never copied (the matching columns of the padded A are zero): keep them finite
+    for (int s = 0; s < STAGES; ++s) {
+      double* Xz = reinterpret_cast<double*>(smem_raw + (size_t)s * D::STAGE_BYTES + D::A_BYTES);
+      for (int i = tid; i < KC * KP; i += D::NTD) Xz[i] = 0.0;
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
   __syncthreads();
-  const int nchunks = n / KC;
+  // split-K: blockIdx.y owns the chunk range [c0, c0 + nchunks) and writes its partial product to slab blockIdx.y of Y
+  const int per_split = (npad / KC + gridDim.y - 1) / gridDim.y;
+  const int c0 = blockIdx.y * per_split;
+  const int nchunks = max(0, min(npad / KC, c0 + per_split) - c0);
+  Y += (size_t)blockIdx.y * (size_t)n * K;
   if (warp == RPT) {  // ---- producer warp: KC slices of A (one per column, contiguous by symmetry) + KC rows of X
     const uint32_t a_line = (uint32_t)(rows * sizeof(double));
     constexpr uint32_t x_line = (uint32_t)(K * sizeof(double));
-    for (int c = 0; c < nchunks; ++c) {
-      const int s = c % STAGES;
-      if (c >= STAGES) mbar_wait(&bar_empty[s], (uint32_t)(((c / STAGES) - 1) & 1));
+    for (int ci = 0; ci < nchunks; ++ci) {
+      const int c = c0 + ci;
+      const int s = ci % STAGES;
+      if (ci >= STAGES) mbar_wait(&bar_empty[s], (uint32_t)(((ci / STAGES) - 1) & 1));
       unsigned char* S = smem_raw + (size_t)s * D::STAGE_BYTES;
-      if (lane == 0) mbar_arrive_expect_tx(&bar_full[s], (uint32_t)(KC * a_line + KC * x_line));
+      const int xr = min(KC, n - c * KC);  // rows of X in this slab (short only in the last chunk of a padded operator)
+      if (lane == 0) mbar_arrive_expect_tx(&bar_full[s], (uint32_t)(KC * a_line + xr * x_line));
       __syncwarp();
       if (lane < KC)
         bulk_g2s(S + (size_t)lane * TRP * sizeof(double), A + (size_t)(c * KC + lane) * ld + row0, a_line, &bar_full[s]);
-      else
+      else if (lane - KC < xr)
         bulk_g2s(S + D::A_BYTES + (size_t)(lane - KC) * KP * sizeof(double), X + (size_t)(c * KC + lane - KC) * K, x_line, &bar_full[s]);
     }
     return;
@@ -209,9 +237,9 @@ __global__ void __launch_bounds__(DmmaTiling<K, RPT>::NTD, DmmaTiling<K, RPT>::C
   for (int mb = 0; mb < 2; ++mb)
 #pragma unroll
     for (int nb = 0; nb < NB; ++nb) acc[mb][nb][0] = acc[mb][nb][1] = 0.0;
-  for (int c = 0; c < nchunks; ++c) {
-    const int s = c % STAGES;
-    mbar_wait(&bar_full[s], (uint32_t)((c / STAGES) & 1));
+  for (int ci = 0; ci < nchunks; ++ci) {
+    const int s = ci % STAGES;
+    mbar_wait(&bar_full[s], (uint32_t)((ci / STAGES) & 1));
     const double* As = reinterpret_cast<const double*>(smem_raw + (size_t)s * D::STAGE_BYTES);
     const double* Xs = reinterpret_cast<const double*>(smem_raw + (size_t)s * D::STAGE_BYTES + D::A_BYTES);
     if (active) {
@@ -235,6 +263,7 @@ __global__ void __launch_bounds__(DmmaTiling<K, RPT>::NTD, DmmaTiling<K, RPT>::C
 #pragma unroll
     for (int mb = 0; mb < 2; ++mb) {
       const int r = row0 + warp * 16 + mb * 8 + g;
+      if (r >= n) continue;
 #pragma unroll
       for (int nb = 0; nb < NB; ++nb) {
         Pack<double, 2> o;
@@ -246,6 +275,34 @@ __global__ void __launch_bounds__(DmmaTiling<K, RPT>::NTD, DmmaTiling<K, RPT>::C
   }
 }
 
+// Y = sum over the split-K slabs (fixed order: deterministic)
+template <typename T>
+__global__ void __launch_bounds__(256) k_sum_slabs(const T* __restrict__ part, int nslab, int64_t len, T* __restrict__ Y) {
+  for (int64_t e = (int64_t)blockIdx.x * 256 + threadIdx.x; e < len; e += (int64_t)gridDim.x * 256) {
+    T s = part[e];
+    for (int j = 1; j < nslab; ++j) s += part[(size_t)j * len + e];
+    Y[e] = s;
+  }
+}
+
+// Small operators leave most SMs idle (n = 1000: 11 row tiles) and every tile walks all n / 16 chunks one bulk-copy
+// latency after the other.  With caller-provided scratch (slq_op_set_scratch) the chunk range is split over gridDim.y
+// CTAs per tile, each writing a partial slab, and k_sum_slabs adds the slabs in order.
+template <typename T, int K>
+static int dense_splits(const slq_op* op, int tile_rows) {
+  if (!op->scratch) return 1;
+  const int64_t npad = op->npad > 0 ? op->npad : op->n;
+  const int64_t tiles = (npad + tile_rows - 1) / tile_rows;
+  const int sms = sm_count() > 0 ? sm_count() : 148;
+  int64_t s = (2 * (int64_t)sms) / tiles;
+  const int64_t nch = npad / 16;
+  if (s > 16) s = 16;
+  if (s > nch / 2) s = nch / 2;  // at least two chunks per split
+  const int64_t fit = (int64_t)(op->scratch_bytes / ((size_t)op->n * K * sizeof(T)));
+  if (s > fit) s = fit;
+  return s < 2 ? 1 : (int)s;
+}
+
 template <int K, int RPT>
 static int launch_dense_dmma_rpt(const slq_op* op, const double* X, double* Y, cudaStream_t st) {
   using D = DmmaTiling<K, RPT>;
@@ -254,9 +311,17 @@ static int launch_dense_dmma_rpt(const slq_op* op, const double* X, double* Y, c
     SLQ_CUDA(cudaFuncSetAttribute(k_dense_dmma<K, RPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)D::SMEM_BYTES));
     once.done();
   }
-  k_dense_dmma<K, RPT><<<(unsigned)((op->n + D::TR - 1) / D::TR), D::NTD, D::SMEM_BYTES, st>>>((int)op->n, (const double*)op->dense, op->ld,
-                                                                                               X, Y);
+  const int64_t npad = op->npad > 0 ? op->npad : op->n;
+  const int splits = dense_splits<double, K>(op, D::TR);
+  dim3 grid((unsigned)((npad + D::TR - 1) / D::TR), (unsigned)splits);
+  k_dense_dmma<K, RPT><<<grid, D::NTD, D::SMEM_BYTES, st>>>((int)op->n, (int)npad, (const double*)op->dense, op->ld, X,
+                                                            splits > 1 ? (double*)op->scratch : Y);
   SLQ_LAUNCH_CHECK();
+  if (splits > 1) {
+    const int64_t len = op->n * K;
+    k_sum_slabs<double><<<(unsigned)std::min<int64_t>((len + 255) / 256, 1024), 256, 0, st>>>((const double*)op->scratch, splits, len, Y);
+    SLQ_LAUNCH_CHECK();
+  }
   return SLQ_OK;
 }
 
@@ -273,7 +338,8 @@ static bool use_dmma() {
 template <typename T, int K>
 static bool dense_tma_ok(const slq_op* op, const T* X, const T* Y) {
   using D = DenseTiling<T, K>;
-  return op->n % D::KC == 0 && op->n >= D::KC && (op->ld * (int64_t)sizeof(T)) % 16 == 0 && op->n < (int64_t)INT32_MAX &&
+  const int64_t npad = op->npad > 0 ? op->npad : op->n;
+  return npad % D::KC == 0 && npad >= D::KC && op->ld >= npad && (op->ld * (int64_t)sizeof(T)) % 16 == 0 && npad < (int64_t)INT32_MAX &&
          (((uintptr_t)op->dense | (uintptr_t)X | (uintptr_t)Y) & 15) == 0;
 }
 
@@ -285,9 +351,17 @@ static int launch_dense_tma_rpt(const slq_op* op, const T* X, T* Y, cudaStream_t
     SLQ_CUDA(cudaFuncSetAttribute(k_dense_tma<T, K, RPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)D::SMEM_BYTES));
     once.done();
   }
-  k_dense_tma<T, K, RPT><<<(unsigned)((op->n + D::TR - 1) / D::TR), D::NTD, D::SMEM_BYTES, st>>>((int)op->n, (const T*)op->dense,
-                                                                                                    op->ld, X, Y);
+  const int64_t npad = op->npad > 0 ? op->npad : op->n;
+  const int splits = dense_splits<T, K>(op, D::TR);
+  dim3 grid((unsigned)((npad + D::TR - 1) / D::TR), (unsigned)splits);
+  k_dense_tma<T, K, RPT><<<grid, D::NTD, D::SMEM_BYTES, st>>>((int)op->n, (int)npad, (const T*)op->dense, op->ld, X,
+                                                             splits > 1 ? (T*)op->scratch : Y);
   SLQ_LAUNCH_CHECK();
+  if (splits > 1) {
+    const int64_t len = op->n * K;
+    k_sum_slabs<T><<<(unsigned)std::min<int64_t>((len + 255) / 256, 1024), 256, 0, st>>>((const T*)op->scratch, splits, len, Y);
+    SLQ_LAUNCH_CHECK();
+  }
   return SLQ_OK;
 }
 
@@ -299,7 +373,7 @@ static int launch_dense_tma(const slq_op* op, const T* X, T* Y, cudaStream_t st)
   int best = 8;
   int64_t best_cost = INT64_MAX;
   for (int rpt = 8; rpt >= 6; --rpt) {
-    const int64_t tiles = (op->n + 16 * rpt - 1) / (16 * rpt);
+    const int64_t tiles = ((op->npad > 0 ? op->npad : op->n) + 16 * rpt - 1) / (16 * rpt);
     const int64_t cost = ((tiles + sms - 1) / sms) * rpt;
     if (cost < best_cost) {
       best_cost = cost;
@@ -311,7 +385,7 @@ static int launch_dense_tma(const slq_op* op, const T* X, T* Y, cudaStream_t st)
   if constexpr (sizeof(T) == 8) {
     if (use_dmma()) {  // fp64: tensor-core tiles, one 16-row slab per consumer warp (TR = 16 RPT as below)
       // one tall CTA per SM (224 rows: 1.8 KB contiguous per bulk copy) when that balances at least as well
-      const int64_t tall = (op->n + 223) / 224;
+      const int64_t tall = ((op->npad > 0 ? op->npad : op->n) + 223) / 224;
       int pick = best;
       if (((tall + sms - 1) / sms) * 14 <= best_cost) pick = 14;
       if (e && (atoi(e) == 14 || (atoi(e) >= 6 && atoi(e) <= 8))) pick = atoi(e);

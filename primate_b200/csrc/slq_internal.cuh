@@ -89,6 +89,9 @@ struct slq_op {
   // dense
   const void* dense;
   int64_t ld;
+  void* scratch;         // optional caller-owned scratch (slq_op_set_scratch): split-K slabs of small dense operators
+  size_t scratch_bytes;
+  int64_t npad;  // 0, or n rounded up to 16: the array is npad x ld with zero rows / columns past n (slq_dense_create_padded)
   // callback
   slq_matmat_fn fn;
   void* ctx;

@@ -120,6 +120,21 @@ int slq_dense_create(int64_t n, const void* A_dev, int64_t ld, int dtype, slq_op
   return SLQ_OK;
 }
 
+int slq_dense_create_padded(int64_t n, int64_t npad, const void* A_dev, int64_t ld, int dtype, slq_op** out) {
+  SLQ_REQUIRE(npad >= n && npad % 16 == 0 && npad - n < 16 && ld >= npad, "npad must be n rounded up to a multiple of 16 and ld >= npad");
+  int rc = slq_dense_create(n, A_dev, ld, dtype, out);
+  if (rc == SLQ_OK) (*out)->npad = npad;
+  return rc;
+}
+
+int slq_op_set_scratch(slq_op* op, void* scratch_dev, size_t bytes) {
+  SLQ_REQUIRE(op != nullptr, "op is NULL");
+  SLQ_REQUIRE(((uintptr_t)scratch_dev & 31) == 0, "scratch must be 32-byte aligned");
+  op->scratch = scratch_dev;
+  op->scratch_bytes = scratch_dev ? bytes : 0;
+  return SLQ_OK;
+}
+
 int slq_callback_create(int64_t n, int dtype, slq_matmat_fn fn, void* ctx, slq_op** out) {
   SLQ_REQUIRE(out != nullptr, "out is NULL");
   SLQ_REQUIRE(n > 0, "invalid shape");

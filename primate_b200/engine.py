@@ -262,10 +262,22 @@ class DeviceOperator:
 		elif isinstance(A, np.ndarray) or (hasattr(A, "is_cuda") and hasattr(A, "data_ptr")):
 			M = A if hasattr(A, "data_ptr") else torch.from_numpy(np.ascontiguousarray(A, dtype=self.dtype))
 			M = M.to(dev, dtype=_tdtype(self.dtype)).contiguous()
-			self._keep = [M]
 			self.h2d_bytes = M.numel() * M.element_size()
 			self.kind, self.nnz = "dense", self.n * self.n
-			_ffi.check(L.slq_dense_create(self.n, M.data_ptr(), self.n, self.code, ctypes.byref(self._handle)))
+			if self.n % 16 and self.n >= 16:
+				# order not a multiple of 16: zero-pad once on the device so that the bulk-copy / tensor-core kernels apply
+				npad = -(-self.n // 16) * 16
+				P = torch.zeros((npad, npad), dtype=M.dtype, device=dev)
+				P[: self.n, : self.n] = M
+				self._keep = [P]
+				_ffi.check(L.slq_dense_create_padded(self.n, npad, P.data_ptr(), npad, self.code, ctypes.byref(self._handle)))
+			else:
+				self._keep = [M]
+				_ffi.check(L.slq_dense_create(self.n, M.data_ptr(), self.n, self.code, ctypes.byref(self._handle)))
+			if self.n <= 16384:  # few row tiles: let the dense kernels split the reduction dimension (16 slabs of n x 64)
+				sc = torch.empty(16 * self.n * MAX_BLOCK * M.element_size(), dtype=torch.uint8, device=dev)
+				self._keep.append(sc)
+				_ffi.check(L.slq_op_set_scratch(self._handle, sc.data_ptr(), sc.numel()))
 		else:
 			if not hasattr(A, "matvec"):
 				raise ValueError("Supplied object is missing 'matvec' attribute.")  # pylinop.h:24

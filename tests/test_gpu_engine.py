@@ -118,7 +118,7 @@ def test_dense_matmat_tiled_path(eng, k, dtype):
 
 
 @pytest.mark.parametrize("rpt", [8, 7, 6])
-@pytest.mark.parametrize("n,k,dtype", [(1232, 32, np.float64), (400, 8, np.float64), (2000, 64, np.float32), (16, 16, np.float64)])
+@pytest.mark.parametrize("n,k,dtype", [(1232, 32, np.float64), (400, 8, np.float64), (2000, 64, np.float32), (16, 16, np.float64), (4096, 32, np.float64)])
 def test_dense_matmat_tile_heights(eng, monkeypatch, rpt, n, k, dtype):
 	"""Every compiled CTA height (128, 112, 96 rows) of the warp-specialised dense kernel, with a short last row tile and
 	more chunks than pipeline stages, against NumPy (SLQ_DENSE_RPT is read at every launch)."""
@@ -129,6 +129,22 @@ def test_dense_matmat_tile_heights(eng, monkeypatch, rpt, n, k, dtype):
 	X = rng.standard_normal((n, k)).astype(dtype)
 	Y = eng.DeviceOperator(D, dtype=dtype).matmat(eng.block_from_columns(X, dtype)).cpu().numpy()
 	ref = D.astype(np.float64) @ X.astype(np.float64)
+	assert np.allclose(Y, ref, rtol=1e-12 if dtype == np.float64 else 2e-4, atol=1e-10 if dtype == np.float64 else 5e-3)
+
+
+@pytest.mark.parametrize("n", [17, 100, 1000, 1231])
+@pytest.mark.parametrize("k,dtype", [(64, np.float64), (8, np.float64), (32, np.float32), (1, np.float64)])
+def test_dense_matmat_any_order_through_padded_tiles(eng, n, k, dtype):
+	"""Orders that are not a multiple of 16 are zero-padded on the device at ingestion and take the bulk-copy kernels
+	(DMMA tiles in fp64): short last X slab, stores stop at n, panels keep n rows."""
+	rng = np.random.default_rng(n + k)
+	D = rng.standard_normal((n, n))
+	D = ((D + D.T) / 2).astype(dtype)
+	X = rng.standard_normal((n, k)).astype(dtype)
+	op = eng.DeviceOperator(D, dtype=dtype)
+	Y = op.matmat(eng.block_from_columns(X, dtype)).cpu().numpy()
+	ref = D.astype(np.float64) @ X.astype(np.float64)
+	assert Y.shape == (n, k) and np.all(np.isfinite(Y))
 	assert np.allclose(Y, ref, rtol=1e-12 if dtype == np.float64 else 2e-4, atol=1e-10 if dtype == np.float64 else 5e-3)
 
 
