@@ -20,6 +20,7 @@ from .tridiag import eigh_tridiag  # noqa: F401
 
 F64: np.dtype = np.dtype("float64")
 BASIS_BUDGET = 40 << 30  # bytes a stored Lanczos basis (deg x n x k) may take before f(A) X goes basis-free
+PANEL_BUDGET = 40 << 30  # bytes the five panels of the basis-free engine may take (narrows the block only for n > 3e7)
 _FORCE_STORED_BASIS = False  # tests / A-B timing: route every f(A) X through the stored-basis formula
 _FORCE_TWOPASS = False  # ... or (orth = 0) through the basis-free two-pass engine
 
@@ -223,9 +224,11 @@ class MatrixFunction(LinearOperator):
 	def _basis_block_width(self, n: int, budget: Optional[int] = None) -> int:
 		"""Widest probe block (power of two <= 32) for f(A) X: the two-pass engine holds five panels whatever `deg` is;
 		the stored-basis path is narrowed until its deg x n x k basis stays within the budget."""
-		budget = BASIS_BUDGET if budget is None else budget
 		itemsize = np.dtype(self.dtype).itemsize
-		per_column = (5 if self._use_twopass(n) else self._deg) * n * itemsize
+		if self._use_twopass(n):  # five panels: its own (fixed) allowance, independent of the basis budget that selected it
+			budget, per_column = (PANEL_BUDGET if budget is None else budget), 5 * n * itemsize
+		else:
+			budget, per_column = (BASIS_BUDGET if budget is None else budget), self._deg * n * itemsize
 		k = 32
 		while k > 1 and k * per_column > budget:
 			k >>= 1
