@@ -246,3 +246,22 @@ def test_update_trinv_and_block_append():
 		assert np.allclose(Rinv, np.linalg.inv(R[: j + 1, : j + 1]), atol=1e-10)
 	blk = append_trinv(np.linalg.inv(R[:5, :5]), R[:5, 5:], np.linalg.inv(R[5:, 5:]))
 	assert np.allclose(blk, np.linalg.inv(R), atol=1e-10)
+
+
+def test_gathered_samples_keep_genuine_nans():
+	"""Multi-rank sample tables are cut by each rank's known share, not by filtering NaN padding: a NaN quadrature sample
+	(an inv / sqrt of a bad Ritz value) reaches the estimator as it would on one rank."""
+	from primate_b200 import trace
+
+	class FakeComm:
+		rank, size, backend = 1, 3, "fake"
+
+		def __init__(self, rows):
+			self.rows = rows
+
+		def all_gather(self, x):
+			return np.stack(self.rows)
+
+	rows = [np.array([1.0, np.nan, 3.0]), np.array([4.0, 5.0, 6.0]), np.array([7.0, 0.0, 0.0])]  # 7 probes over 3 ranks: 3 + 3 + 1
+	got = trace._gather_ranges(rows[1], 7, FakeComm(rows))
+	assert got.shape == (7,) and np.isnan(got[1]) and np.array_equal(got[[0, 2, 3, 4, 5, 6]], [1.0, 3.0, 4.0, 5.0, 6.0, 7.0])

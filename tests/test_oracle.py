@@ -164,3 +164,69 @@ def test_ref_matvec_matches_reference_golden(oracle, golden):
 			y = oracle.ref_matvec(A, v, fun, deg=20, orth=orth, **kw)
 			g = golden[f"matvec_{fun}_orth{orth}_v42"]
 			assert np.max(np.abs(y - np.ravel(g))) < 1e-12 * np.max(np.abs(g))
+
+
+def test_ziggurat_restatement_and_tables_match_installed_numpy():
+	"""oracle/zig_oracle.py (NumPy's random_standard_normal restated on the raw PCG64 stream, tables from
+	tests/golden/ziggurat_tables.npz) reproduces Generator.standard_normal bit for bit, with the same number of raw draws;
+	the committed tables are the installed NumPy's (the header compiled into libslq carries the same arrays)."""
+	import os
+	import re
+
+	from oracle import zig_oracle
+
+	ki, wi, fi = zig_oracle.tables()
+	assert ki.shape == wi.shape == fi.shape == (256,) and ki[1] == 0 and fi[0] == 1.0
+	for seed, n in ((0, 120_000), (99, 50_000)):
+		got, used = zig_oracle.np_standard_normal(seed, n)
+		g = np.random.default_rng(seed)
+		ref = g.standard_normal(n)
+		assert np.array_equal(got, ref)
+		chk = np.random.default_rng(seed)
+		chk.bit_generator.advance(used)
+		assert chk.bit_generator.state == g.bit_generator.state and used > n
+	root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+	hdr = open(os.path.join(root, "primate_b200", "csrc", "slq_ziggurat_tables.h")).read()
+	words = [int(w, 16) for w in re.findall(r"0x([0-9A-F]{16})ull", hdr)]
+	assert len(words) == 768
+	assert np.array_equal(np.array(words[:256], dtype=np.uint64), ki)
+	assert np.array_equal(np.array(words[256:512], dtype=np.uint64), wi.view(np.uint64))
+	assert np.array_equal(np.array(words[512:], dtype=np.uint64), fi.view(np.uint64))
+
+
+def test_pairwise_plan_reproduces_numpy_column_sums():
+	"""primate_b200.random._pairwise_plan (the stack-machine form of NumPy's pairwise summation the sphere kernels replay)
+	gives np.sum's bits for column sums of an F-ordered array (random.py:38: np.sum(out**2, axis=0))."""
+	from primate_b200.random import _pairwise_plan
+
+	def leaf(a):
+		if len(a) < 8:
+			res = 0.0
+			for x in a:
+				res += x
+			return res
+		r = list(a[:8])
+		i = 8
+		while i < len(a) - (len(a) % 8):
+			for j in range(8):
+				r[j] += a[i + j]
+			i += 8
+		res = ((r[0] + r[1]) + (r[2] + r[3])) + ((r[4] + r[5]) + (r[6] + r[7]))
+		for x in a[i:]:
+			res += x
+		return res
+
+	rng = np.random.default_rng(3)
+	for n in (5, 8, 129, 1000, 4097, 70_001):
+		W = np.empty((n, 2), order="F")
+		rng.standard_normal(out=W)
+		sq = (W**2)[:, 1].tolist()
+		starts, lens, red = _pairwise_plan(n)
+		assert lens.sum() == n and red.sum() == len(starts) - 1
+		stack = []
+		for a, b, c in zip(starts, lens, red):
+			stack.append(leaf(sq[a : a + b]))
+			for _ in range(c):
+				y, x = stack.pop(), stack.pop()
+				stack.append(x + y)
+		assert len(stack) == 1 and stack[0] == float(np.sum(W**2, axis=0)[1])
