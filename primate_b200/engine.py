@@ -147,8 +147,6 @@ def _device_csr_from(A, dtype, dev):
 	v = v[order].to(tdt)
 	uniq, inverse = torch.unique_consecutive(key, return_inverse=True)
 	vals = torch.zeros(uniq.numel(), dtype=tdt, device=dev).index_add_(0, inverse, v)
-	if A.format == "bsr":  # SciPy keeps explicit zeros of stored blocks; so do we (same operator either way)
-		pass
 	rows = uniq // n
 	rowptr = torch.zeros(n + 1, dtype=torch.int64, device=dev)
 	rowptr[1:] = torch.cumsum(torch.bincount(rows, minlength=n), 0)
