@@ -101,6 +101,15 @@ int slq_dense_create_padded(int64_t n, int64_t npad, const void* A_dev, int64_t 
  * the reduction dimension of Y = A X over several CTAs per row tile (partial slabs of n x k, summed in a fixed order):
  * 16 n k sizeof(T) bytes allow the full split.  Calls that use the scratch must not overlap on different streams. */
 int slq_op_set_scratch(slq_op* op, void* scratch_dev, size_t bytes);
+/* Optional band-major copy of an fp64 dense operator for the tensor-core product kernel (the caller owns the buffer; it
+ * must outlive the operator or be detached with buf_dev = NULL).  slq_dense_tiled_bytes reports the size (0 when the
+ * operator does not take that kernel: fp32, order not a multiple of 16 and not created padded); slq_dense_set_tiled
+ * fills the buffer on `stream` (one pass over A) and switches Y = A X to it.  Row-major A makes every pipeline stage 16
+ * strided lines of 1.8 KB and DRAM page conflicts hold the product at 4.2 TB/s (so is cuBLAS DGEMM on the same operand);
+ * the copy stores each stage image contiguously, one bulk copy per stage, 148 sequential streams.  Results are bit-identical
+ * with and without it.  Replaces the per-call column-major copy of include/eigen_operators.h:24-30 (made once here). */
+int slq_dense_tiled_bytes(const slq_op* op, size_t* bytes);
+int slq_dense_set_tiled(slq_op* op, void* buf_dev, size_t bytes, slq_stream stream);
 /* Matrix-free operator driven by a callback (device panels in, device panels out). */
 int slq_callback_create(int64_t n, int dtype, slq_matmat_fn fn, void* ctx, slq_op** out);
 int slq_op_destroy(slq_op* op);

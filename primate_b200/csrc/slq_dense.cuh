@@ -180,7 +180,13 @@ __device__ __forceinline__ void dmma_884(double (&c)[2], double a, double b) {
   asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c[0]), "+d"(c[1]) : "d"(a), "d"(b));
 }
 
-template <int K, int RPT>
+//
+// TILED: A points at the band-major copy made by slq_dense_set_tiled (dense_tiled_elems): the stage image of chunk c of
+// this CTA's band is ONE contiguous 16 x TRP block, fetched by one bulk copy, and a CTA walks its band front to back --
+// 148 sequential streams through HBM.  Reading the row-major operator instead costs KC strided 1.8 KB lines per stage,
+// ~112 matrix rows open per CTA at a time: DRAM page conflicts hold that form (and cuBLAS DGEMM on the same operand) at
+// 4.2 TB/s where a stream reads 6.9 TB/s (profiles/r02c_dense_tiled.md).  Same arithmetic in the same order either way.
+template <int K, int RPT, bool TILED>
 __global__ void __launch_bounds__(DmmaTiling<K, RPT>::NTD, DmmaTiling<K, RPT>::CTAS)
     k_dense_dmma(int n, int npad, const double* __restrict__ A, int64_t ld, const double* __restrict__ X, double* __restrict__ Y) {
   using D = DmmaTiling<K, RPT>;
@@ -220,12 +226,22 @@ __global__ void __launch_bounds__(DmmaTiling<K, RPT>::NTD, DmmaTiling<K, RPT>::C
       if (ci >= STAGES) mbar_wait(&bar_empty[s], (uint32_t)(((ci / STAGES) - 1) & 1));
       unsigned char* S = smem_raw + (size_t)s * D::STAGE_BYTES;
       const int xr = min(KC, n - c * KC);  // rows of X in this slab (short only in the last chunk of a padded operator)
+      if constexpr (TILED) {
+        if (lane == 0) {
+          mbar_arrive_expect_tx(&bar_full[s], (uint32_t)(D::A_BYTES + xr * x_line));
+          bulk_g2s(S, A + ((size_t)blockIdx.x * (size_t)(npad / KC) + (size_t)c) * (size_t)(KC * TRP), (uint32_t)D::A_BYTES, &bar_full[s]);
+        }
+        __syncwarp();
+        if (lane >= KC && lane - KC < xr)
+          bulk_g2s(S + D::A_BYTES + (size_t)(lane - KC) * KP * sizeof(double), X + (size_t)(c * KC + lane - KC) * K, x_line, &bar_full[s]);
+      } else {
       if (lane == 0) mbar_arrive_expect_tx(&bar_full[s], (uint32_t)(KC * a_line + xr * x_line));
       __syncwarp();
       if (lane < KC)
         bulk_g2s(S + (size_t)lane * TRP * sizeof(double), A + (size_t)(c * KC + lane) * ld + row0, a_line, &bar_full[s]);
       else if (lane - KC < xr)
         bulk_g2s(S + D::A_BYTES + (size_t)(lane - KC) * KP * sizeof(double), X + (size_t)(c * KC + lane - KC) * K, x_line, &bar_full[s]);
+      }
     }
     return;
   }
@@ -308,14 +324,19 @@ static int launch_dense_dmma_rpt(const slq_op* op, const double* X, double* Y, c
   using D = DmmaTiling<K, RPT>;
   static DeviceOnce once;
   if (once.needed()) {
-    SLQ_CUDA(cudaFuncSetAttribute(k_dense_dmma<K, RPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)D::SMEM_BYTES));
+    SLQ_CUDA(cudaFuncSetAttribute(k_dense_dmma<K, RPT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)D::SMEM_BYTES));
+    SLQ_CUDA(cudaFuncSetAttribute(k_dense_dmma<K, RPT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)D::SMEM_BYTES));
     once.done();
   }
   const int64_t npad = op->npad > 0 ? op->npad : op->n;
   const int splits = dense_splits<double, K>(op, D::TR);
   dim3 grid((unsigned)((npad + D::TR - 1) / D::TR), (unsigned)splits);
-  k_dense_dmma<K, RPT><<<grid, D::NTD, D::SMEM_BYTES, st>>>((int)op->n, (int)npad, (const double*)op->dense, op->ld, X,
-                                                            splits > 1 ? (double*)op->scratch : Y);
+  if (op->tiled && op->tiled_rpt == RPT)
+    k_dense_dmma<K, RPT, true><<<grid, D::NTD, D::SMEM_BYTES, st>>>((int)op->n, (int)npad, (const double*)op->tiled, op->ld, X,
+                                                                    splits > 1 ? (double*)op->scratch : Y);
+  else
+    k_dense_dmma<K, RPT, false><<<grid, D::NTD, D::SMEM_BYTES, st>>>((int)op->n, (int)npad, (const double*)op->dense, op->ld, X,
+                                                                     splits > 1 ? (double*)op->scratch : Y);
   SLQ_LAUNCH_CHECK();
   if (splits > 1) {
     const int64_t len = op->n * K;
@@ -323,16 +344,6 @@ static int launch_dense_dmma_rpt(const slq_op* op, const double* X, double* Y, c
     SLQ_LAUNCH_CHECK();
   }
   return SLQ_OK;
-}
-
-// SLQ_DENSE=fma keeps the scalar-FMA kernel for fp64 too (A/B timing and parity of the two summation orders).
-static bool use_dmma() {
-  static int cached = -1;
-  if (cached < 0) {
-    const char* e = getenv("SLQ_DENSE");
-    cached = (e && strcmp(e, "fma") == 0) ? 0 : 1;
-  }
-  return cached == 1;
 }
 
 template <typename T, int K>
@@ -365,39 +376,21 @@ static int launch_dense_tma_rpt(const slq_op* op, const T* X, T* Y, cudaStream_t
   return SLQ_OK;
 }
 
-// CTA height: the SM with the most row tiles sets the kernel time, so minimise (tiles per SM, rounded up) x (rows per
-// tile) over the compiled heights; ties go to the taller tile (fewer X slabs re-read from L2).
+// CTA height: dense_pick_rpt (slq_lanczos_common.cuh), the same rule the band-major copy was laid out with.
 template <typename T, int K>
 static int launch_dense_tma(const slq_op* op, const T* X, T* Y, cudaStream_t st) {
-  const int sms = sm_count() > 0 ? sm_count() : 148;
-  int best = 8;
-  int64_t best_cost = INT64_MAX;
-  for (int rpt = 8; rpt >= 6; --rpt) {
-    const int64_t tiles = ((op->npad > 0 ? op->npad : op->n) + 16 * rpt - 1) / (16 * rpt);
-    const int64_t cost = ((tiles + sms - 1) / sms) * rpt;
-    if (cost < best_cost) {
-      best_cost = cost;
-      best = rpt;
-    }
-  }
-  const char* e = getenv("SLQ_DENSE_RPT");  // A/B timing only
-  if (e && atoi(e) >= 6 && atoi(e) <= 8) best = atoi(e);
+  const int64_t npad = op->npad > 0 ? op->npad : op->n;
   if constexpr (sizeof(T) == 8) {
-    if (use_dmma()) {  // fp64: tensor-core tiles, one 16-row slab per consumer warp (TR = 16 RPT as below)
-      // one tall CTA per SM (224 rows: 1.8 KB contiguous per bulk copy) when that balances at least as well
-      const int64_t tall = ((op->npad > 0 ? op->npad : op->n) + 223) / 224;
-      int pick = best;
-      if (((tall + sms - 1) / sms) * 14 <= best_cost) pick = 14;
-      if (e && (atoi(e) == 14 || (atoi(e) >= 6 && atoi(e) <= 8))) pick = atoi(e);
-      if (pick == 14) return launch_dense_dmma_rpt<K, 14>(op, (const double*)X, (double*)Y, st);
-      switch (best) {
+    if (dense_use_dmma()) {  // fp64: tensor-core tiles, one 16-row slab per consumer warp (TR = 16 RPT)
+      switch (dense_pick_rpt(npad, true)) {
+        case 14: return launch_dense_dmma_rpt<K, 14>(op, (const double*)X, (double*)Y, st);
         case 6: return launch_dense_dmma_rpt<K, 6>(op, (const double*)X, (double*)Y, st);
         case 7: return launch_dense_dmma_rpt<K, 7>(op, (const double*)X, (double*)Y, st);
         default: return launch_dense_dmma_rpt<K, 8>(op, (const double*)X, (double*)Y, st);
       }
     }
   }
-  switch (best) {
+  switch (dense_pick_rpt(npad, false)) {
     case 6: return launch_dense_tma_rpt<T, K, 6>(op, X, Y, st);
     case 7: return launch_dense_tma_rpt<T, K, 7>(op, X, Y, st);
     default: return launch_dense_tma_rpt<T, K, 8>(op, X, Y, st);

@@ -135,6 +135,59 @@ int slq_op_set_scratch(slq_op* op, void* scratch_dev, size_t bytes) {
   return SLQ_OK;
 }
 
+namespace slq {
+// one CTA per (chunk, band): the 16 x TRP stage image of the tensor-core kernel, read from 16 contiguous matrix rows
+__global__ void __launch_bounds__(256) k_dense_tile(const double* __restrict__ A, int64_t ld, int64_t npad, int tr, double* __restrict__ out) {
+  const int trp = tr + 4;
+  const int64_t c = blockIdx.x, b = blockIdx.y;
+  const int64_t row0 = b * tr;
+  double* dst = out + ((size_t)b * (size_t)(npad / DENSE_KC) + (size_t)c) * (size_t)(DENSE_KC * trp);
+  for (int idx = threadIdx.x; idx < DENSE_KC * trp; idx += 256) {
+    const int kk = idx / trp, r = idx % trp;
+    double v = 0.0;
+    if (r < tr && row0 + r < npad) v = A[(size_t)(c * DENSE_KC + kk) * ld + row0 + r];
+    dst[idx] = v;
+  }
+}
+
+static bool dense_tiling_applies(const slq_op* op) {
+  if (!op || op->kind != OP_DENSE || op->dtype != SLQ_F64 || !dense_use_dmma()) return false;
+  const int64_t npad = op->npad > 0 ? op->npad : op->n;
+  return npad % DENSE_KC == 0 && npad >= DENSE_KC && npad < (int64_t)INT32_MAX && op->ld >= npad;
+}
+}  // namespace slq
+
+int slq_dense_tiled_bytes(const slq_op* op, size_t* bytes) {
+  SLQ_REQUIRE(op != nullptr && bytes != nullptr, "NULL argument");
+  *bytes = 0;
+  if (!slq::dense_tiling_applies(op)) return SLQ_OK;
+  const int64_t npad = op->npad > 0 ? op->npad : op->n;
+  *bytes = slq::dense_tiled_elems(npad, slq::dense_pick_rpt(npad, true)) * sizeof(double);
+  return SLQ_OK;
+}
+
+int slq_dense_set_tiled(slq_op* op, void* buf_dev, size_t bytes, slq_stream stream) {
+  SLQ_REQUIRE(op != nullptr, "op is NULL");
+  if (!buf_dev) {  // detach
+    op->tiled = nullptr;
+    op->tiled_rpt = 0;
+    return SLQ_OK;
+  }
+  SLQ_REQUIRE(slq::dense_tiling_applies(op), "the band-major copy applies to fp64 dense operators whose (padded) order is a multiple of 16");
+  SLQ_REQUIRE(((uintptr_t)buf_dev & 127) == 0, "buffer must be 128-byte aligned");
+  const int64_t npad = op->npad > 0 ? op->npad : op->n;
+  const int rpt = slq::dense_pick_rpt(npad, true);
+  const size_t need = slq::dense_tiled_elems(npad, rpt) * sizeof(double);
+  SLQ_REQUIRE(bytes >= need, "buffer too small: %zu bytes needed (slq_dense_tiled_bytes)", need);
+  const int64_t tr = 16 * rpt;
+  dim3 grid((unsigned)(npad / slq::DENSE_KC), (unsigned)((npad + tr - 1) / tr));
+  slq::k_dense_tile<<<grid, 256, 0, (cudaStream_t)stream>>>((const double*)op->dense, op->ld, npad, (int)tr, (double*)buf_dev);
+  SLQ_LAUNCH_CHECK();
+  op->tiled = buf_dev;
+  op->tiled_rpt = rpt;
+  return SLQ_OK;
+}
+
 int slq_callback_create(int64_t n, int dtype, slq_matmat_fn fn, void* ctx, slq_op** out) {
   SLQ_REQUIRE(out != nullptr, "out is NULL");
   SLQ_REQUIRE(n > 0, "invalid shape");

@@ -1,7 +1,9 @@
 // Declarations shared by the Lanczos translation units (driver templates are instantiated per scalar type in
 // slq_lanczos_f64.cu / slq_lanczos_f32.cu so that the two halves compile in parallel).
 #pragma once
+#include <climits>
 #include <cmath>
+#include <cstdint>
 #include <cstdlib>
 #include <cstring>
 #include <limits>
@@ -64,6 +66,55 @@ inline size_t ws_layout(int64_t n, int k, int ncv, int dtype, Workspace* ws, cha
     ws->partial = reinterpret_cast<double*>(base + partial_off);
   }
   return off;
+}
+
+// ---- dense operator tiling shared by the kernels (slq_dense.cuh) and the band-major copy (slq_dense_set_tiled) --------
+constexpr int DENSE_KC = 16;  // columns of A (rows of X) per pipeline stage
+
+// SLQ_DENSE=fma keeps the scalar-FMA kernel for fp64 too (A/B timing and parity of the two summation orders).
+inline bool dense_use_dmma() {
+  static int cached = -1;
+  if (cached < 0) {
+    const char* e = getenv("SLQ_DENSE");
+    cached = (e && strcmp(e, "fma") == 0) ? 0 : 1;
+  }
+  return cached == 1;
+}
+
+// CTA height of the dense kernels in units of 16 rows.  The SM with the most row tiles sets the kernel time, so minimise
+// (tiles per SM, rounded up) x (rows per tile) over the compiled heights 6 / 7 / 8 (two CTAs per SM); ties go to the
+// taller tile (fewer X slabs re-read from L2).  The fp64 tensor-core kernel also has a 224-row CTA (one per SM, 1.8 KB
+// contiguous per matrix row) which is taken when it balances at least as well.  SLQ_DENSE_RPT overrides (A/B timing).
+inline int dense_pick_rpt(int64_t npad, bool dmma) {
+  const int sms = sm_count() > 0 ? sm_count() : 148;
+  int best = 8;
+  int64_t best_cost = INT64_MAX;
+  for (int rpt = 8; rpt >= 6; --rpt) {
+    const int64_t tiles = (npad + 16 * rpt - 1) / (16 * rpt);
+    const int64_t cost = ((tiles + sms - 1) / sms) * rpt;
+    if (cost < best_cost) {
+      best_cost = cost;
+      best = rpt;
+    }
+  }
+  if (dmma) {
+    const int64_t tall = (npad + 223) / 224;
+    if (((tall + sms - 1) / sms) * 14 <= best_cost) best = 14;
+  }
+  const char* e = getenv("SLQ_DENSE_RPT");
+  if (e) {
+    const int v = atoi(e);
+    if ((v >= 6 && v <= 8) || (dmma && v == 14)) best = v;
+  }
+  return best;
+}
+
+// Band-major copy: band b = rows [b TR, (b + 1) TR) of the (symmetric) operator, TR = 16 rpt; within a band the chunks
+// c = columns [16 c, 16 c + 16) follow each other, each stored as the shared-memory image of the tensor-core kernel's
+// stage: 16 lines of TRP = TR + 4 doubles, line kk = A[16 c + kk][b TR .. b TR + TR) (zeros past npad and in the pad).
+inline size_t dense_tiled_elems(int64_t npad, int rpt) {
+  const int64_t tr = 16 * rpt;
+  return (size_t)((npad + tr - 1) / tr) * (size_t)(npad / DENSE_KC) * (size_t)DENSE_KC * (size_t)(tr + 4);
 }
 
 // instantiated for float and double in slq_lanczos_f32.cu / slq_lanczos_f64.cu

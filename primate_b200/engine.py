@@ -180,6 +180,9 @@ class DeviceOperator:
 	matrix/array (any format; converted to CSR once, not per call), or any object with `.matvec` and `.shape`
 	(slow host-callback path, include/pylinop.h:17-40).  The matrix is uploaded ONCE per operator.
 
+	`tiled` (dense fp64 input): keep a band-major copy of the matrix for the tensor-core product kernel ("auto": when it
+	fits comfortably; False: row-major only; results are bit-identical either way).
+
 	`reorder` (sparse input): "auto" picks a symmetric row/column order for large operators -- breadth-first locality
 	clusters of one SpMM row tile for meshes and the like, or, when the row lengths are heavily skewed (graph hubs),
 	rows dealt to the tiles by decreasing length so that every tile carries the same number of non-zeros
@@ -187,7 +190,7 @@ class DeviceOperator:
 	order is internal: every vector that crosses the API is in the caller's row order.
 	"""
 
-	def __init__(self, A: Any, dtype=None, reorder="auto"):
+	def __init__(self, A: Any, dtype=None, reorder="auto", tiled="auto"):
 		import scipy.sparse as sp
 
 		torch = _torch()
@@ -202,6 +205,7 @@ class DeviceOperator:
 		self._keep = []
 		self._handle = ctypes.c_void_p()
 		self.h2d_bytes = 0
+		self.tiled = False
 		dev = torch.device("cuda", torch.cuda.current_device())
 		if sp.issparse(A) and A.format in ("coo", "bsr") and not (isinstance(reorder, int) and not isinstance(reorder, bool) and reorder > 1) \
 				and reorder is not True and not _want_reorder(reorder, self.n, int(A.nnz)):
@@ -259,7 +263,10 @@ class DeviceOperator:
 			                               int(np.diff(C.indptr).max(initial=0)), None, ctypes.byref(self._handle)))  # fmt: skip
 		elif isinstance(A, np.ndarray) or (hasattr(A, "is_cuda") and hasattr(A, "data_ptr")):
 			M = A if hasattr(A, "data_ptr") else torch.from_numpy(np.ascontiguousarray(A, dtype=self.dtype))
-			M = M.to(dev, dtype=_tdtype(self.dtype)).contiguous()
+			M = M.to(dev, dtype=_tdtype(self.dtype))
+			if not (M.stride(1) == 1 and M.stride(0) >= self.n and (M.stride(0) * M.element_size()) % 16 == 0):
+				M = M.contiguous()  # (a row-major view with a row stride > n, e.g. columns [0, n) of a wider buffer, is used as it is)
+			ld = int(M.stride(0))
 			self.h2d_bytes = M.numel() * M.element_size()
 			self.kind, self.nnz = "dense", self.n * self.n
 			if self.n % 16 and self.n >= 16:
@@ -271,7 +278,16 @@ class DeviceOperator:
 				_ffi.check(L.slq_dense_create_padded(self.n, npad, P.data_ptr(), npad, self.code, ctypes.byref(self._handle)))
 			else:
 				self._keep = [M]
-				_ffi.check(L.slq_dense_create(self.n, M.data_ptr(), self.n, self.code, ctypes.byref(self._handle)))
+				_ffi.check(L.slq_dense_create(self.n, M.data_ptr(), ld, self.code, ctypes.byref(self._handle)))
+			# fp64: band-major copy for the tensor-core kernel (one contiguous bulk copy per stage instead of 16 strided lines;
+			# the row-major original stays for the narrow-block kernels).  "auto": when the copy fits in a quarter of free HBM.
+			need = ctypes.c_size_t(0)
+			_ffi.check(L.slq_dense_tiled_bytes(self._handle, ctypes.byref(need)))
+			if tiled and need.value and (tiled is True or need.value <= torch.cuda.mem_get_info()[0] // 4):
+				tb = torch.empty(need.value, dtype=torch.uint8, device=dev)
+				self._keep.append(tb)
+				_ffi.check(L.slq_dense_set_tiled(self._handle, tb.data_ptr(), tb.numel(), _stream_ptr()))
+				self.tiled = True
 			if self.n <= 16384:  # few row tiles: let the dense kernels split the reduction dimension (16 slabs of n x 64)
 				sc = torch.empty(16 * self.n * MAX_BLOCK * M.element_size(), dtype=torch.uint8, device=dev)
 				self._keep.append(sc)

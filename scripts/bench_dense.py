@@ -16,6 +16,8 @@ def main():
 	ap.add_argument("--n", type=int, default=32768)
 	ap.add_argument("--k", type=int, default=32)
 	ap.add_argument("--reps", type=int, default=10)
+	ap.add_argument("--row-major", action="store_true", help="no band-major copy (DeviceOperator(tiled=False))")
+	ap.add_argument("--ld-pad", type=int, default=0, help="row stride of A = n + this many elements (power-of-two strides vs HBM channel hashing)")
 	args = ap.parse_args()
 	import torch
 
@@ -25,8 +27,13 @@ def main():
 	g = torch.Generator(device="cuda").manual_seed(0)
 	A = torch.randn((n, n), generator=g, device="cuda", dtype=torch.float64)
 	A = (A + A.T) / 2
+	if args.ld_pad:
+		W = torch.zeros((n, n + args.ld_pad), device="cuda", dtype=torch.float64)
+		W[:, :n] = A
+		del A
+		A = W[:, :n]
 	X = torch.randn((n, k), generator=g, device="cuda", dtype=torch.float64)
-	op = engine.DeviceOperator(A, dtype=np.float64)
+	op = engine.DeviceOperator(A, dtype=np.float64, tiled=not args.row_major)
 
 	def timed(fn):
 		for _ in range(3):
@@ -44,7 +51,7 @@ def main():
 	Yref, ms_blas = timed(lambda: torch.matmul(A, X))
 	err = ((Y - Yref).abs().max() / Yref.abs().max()).item()
 	flops = 2.0 * n * n * k
-	print(json.dumps({"n": n, "k": k, "kernel": os.environ.get("SLQ_DENSE", "dmma"), "ms": ms, "tflops": flops / ms / 1e9,
+	print(json.dumps({"n": n, "k": k, "ld_pad": args.ld_pad, "tiled": op.tiled, "kernel": os.environ.get("SLQ_DENSE", "dmma"), "ms": ms, "tflops": flops / ms / 1e9,
 	                  "cublas_ms": ms_blas, "cublas_tflops": flops / ms_blas / 1e9, "vs_cublas": ms_blas / ms, "rel_err_vs_cublas": err}))  # fmt: skip
 
 
