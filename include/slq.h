@@ -270,6 +270,20 @@ size_t slq_panel_coldot_workspace_bytes(int m);
 int slq_panel_coldot(const void* X_dev, int64_t ldx, const void* Y_dev, int64_t ldy, int m, int64_t row0, int64_t row1, int dtype,
                      double* out_dev, void* workspace_dev, size_t workspace_bytes, slq_stream stream);
 
+/* Allocation-free variant of slq_panel_coldot.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot allocate device memory (CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  Same kernels, same result (bit-identical to slq_panel_coldot: same grid, same summation order),
+ * but the per-CTA partial table lives in a static __device__ array inside the library instead of a caller workspace:
+ * 512 x 256 doubles = 1 MiB held by every GPU that loads the library until the process exits.  Limit:
+ * m <= SLQ_COLDOT_STATIC_MAX_M (256); a larger m is rejected with SLQ_ERR_ARG and a message naming the limit.  The
+ * call allocates and frees nothing (the first call on a device looks the array's device address up with
+ * cudaGetSymbolAddress).  ALL calls on a device share the one array and it keeps the last call's
+ * contents: nothing needs to start at zero (every entry read is written first by the same call), but two calls that
+ * overlap on the GPU (different streams, no ordering between them) RACE on it -- serialise them. */
+#define SLQ_COLDOT_STATIC_MAX_M 256
+int slq_panel_coldot_static(const void* X_dev, int64_t ldx, const void* Y_dev, int64_t ldy, int m, int64_t row0, int64_t row1,
+                            int dtype, double* out_dev, slq_stream stream);
+
 #if defined(__GNUC__)
 #pragma GCC visibility pop
 #endif

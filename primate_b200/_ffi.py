@@ -85,6 +85,7 @@ _SIGNATURES = {
 	"slq_panel_coldot_workspace_bytes": (c_size_t, [c_int]),
 	"slq_panel_coldot": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int, c_int64, c_int64, c_int, c_void_p, c_void_p, c_size_t,
 	                             c_void_p]),
+	"slq_panel_coldot_static": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int, c_int64, c_int64, c_int, c_void_p, c_void_p]),
 	"slq_basis_combine": (c_int, [c_void_p, c_int64, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
 }  # fmt: skip
 

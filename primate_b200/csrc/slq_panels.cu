@@ -9,6 +9,7 @@
 // Panels are row-major with a row stride (ld), so column ranges of a wider buffer are panels too.  All reductions are
 // deterministic (per-CTA partial tables summed in a fixed order), accumulate in fp64 and return fp64.
 #include <algorithm>
+#include <atomic>
 #include <cstdlib>
 #include <cstring>
 #include <type_traits>
@@ -337,6 +338,31 @@ __global__ void k_coldot_reduce(const double* __restrict__ partial, int nparts, 
   out[j] = s;
 }
 
+// ---- allocation-free column dots (slq_panel_coldot_static) -------------------------------------------------------------
+// The per-CTA partial table of k_panel_coldot lives in a file-scope device array instead of a caller workspace: 1 MiB
+// that every GPU loading the library holds until the process exits.  In HOST code `g_coldot_static` is only a stand-in
+// for the symbol, not a device address: the address is looked up once per device (cudaGetSymbolAddress with that
+// device current) and passed to the kernels as an ordinary pointer.
+constexpr int COLDOT_STATIC_MAX_M = SLQ_COLDOT_STATIC_MAX_M;  // widest panel the static table serves (include/slq.h)
+constexpr int COLDOT_STATIC_MAX_PARTS = 512;  // most CTAs (partial rows) of one call
+static __device__ __align__(256) double g_coldot_static[(size_t)COLDOT_STATIC_MAX_PARTS * COLDOT_STATIC_MAX_M];
+
+static int coldot_static_ptr(double** out) {
+  static std::atomic<double*> addr[MAX_DEVICES];  // zero-initialised: nullptr = not looked up on that device yet
+  const int dev = current_device();
+  if (dev < 0 || dev >= MAX_DEVICES) return fail(SLQ_ERR_CUDA, "no current CUDA device (or ordinal >= %d)", MAX_DEVICES);
+  double* p = addr[dev].load(std::memory_order_acquire);
+  if (!p) {  // two threads may both look it up: same answer
+    void* sym = nullptr;
+    SLQ_CUDA(cudaGetSymbolAddress(&sym, g_coldot_static));
+    if (!sym) return fail(SLQ_ERR_CUDA, "cudaGetSymbolAddress returned a null address");
+    p = (double*)sym;
+    addr[dev].store(p, std::memory_order_release);
+  }
+  *out = p;
+  return SLQ_OK;
+}
+
 static int gram_grid(int64_t nrows) {
   const int sms = sm_count() > 0 ? sm_count() : 148;
   const int64_t chunks = (nrows + PG_RC - 1) / PG_RC;
@@ -495,6 +521,36 @@ int slq_panel_coldot(const void* X_dev, int64_t ldx, const void* Y_dev, int64_t 
   }
   const int g = (int)std::max<int64_t>(1, std::min<int64_t>((row1 - row0 + 63) / 64, 2 * (int64_t)sms));
   double* partial = (double*)workspace_dev;
+  if (dtype == SLQ_F64)
+    k_panel_coldot<double><<<g, 256, 0, st>>>((const double*)X_dev, ldx, (const double*)Y_dev, ldy, m, row0, row1, partial);
+  else
+    k_panel_coldot<float><<<g, 256, 0, st>>>((const float*)X_dev, ldx, (const float*)Y_dev, ldy, m, row0, row1, partial);
+  SLQ_LAUNCH_CHECK();
+  k_coldot_reduce<<<(m + 127) / 128, 128, 0, st>>>(partial, g, m, out_dev);
+  SLQ_LAUNCH_CHECK();
+  return SLQ_OK;
+}
+
+int slq_panel_coldot_static(const void* X_dev, int64_t ldx, const void* Y_dev, int64_t ldy, int m, int64_t row0, int64_t row1, int dtype,
+                            double* out_dev, slq_stream stream) {
+  SLQ_REQUIRE(X_dev && Y_dev && out_dev && m > 0 && row1 >= row0 && ldx >= m && ldy >= m, "invalid argument");
+  SLQ_REQUIRE(dtype == SLQ_F32 || dtype == SLQ_F64, "Only 32- or 64-bit floats are supported.");
+  SLQ_REQUIRE(m <= COLDOT_STATIC_MAX_M, "m = %d exceeds the static scratch of slq_panel_coldot_static (at most %d columns); "
+              "use slq_panel_coldot with a caller workspace", m, COLDOT_STATIC_MAX_M);
+  const int sms = sm_count();
+  if (sms <= 0) return fail(SLQ_ERR_CUDA, "no CUDA device");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (row1 == row0) {
+    SLQ_CUDA(cudaMemsetAsync(out_dev, 0, sizeof(double) * m, st));
+    return SLQ_OK;
+  }
+  double* partial = nullptr;
+  int rc = coldot_static_ptr(&partial);
+  if (rc != SLQ_OK) return rc;
+  // same grid rule as slq_panel_coldot (so the two entry points sum in the same order), capped by the table's rows;
+  // every partial entry the reduction reads is written by this call's first kernel, so nothing needs clearing
+  int g = (int)std::max<int64_t>(1, std::min<int64_t>((row1 - row0 + 63) / 64, 2 * (int64_t)sms));
+  if (g > COLDOT_STATIC_MAX_PARTS) g = COLDOT_STATIC_MAX_PARTS;
   if (dtype == SLQ_F64)
     k_panel_coldot<double><<<g, 256, 0, st>>>((const double*)X_dev, ldx, (const double*)Y_dev, ldy, m, row0, row1, partial);
   else
