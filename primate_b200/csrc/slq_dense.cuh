@@ -169,9 +169,20 @@ struct DmmaTiling {
   static constexpr size_t STAGE_BYTES = A_BYTES + X_BYTES;
   static constexpr int STAGES_FIT = (int)(((CTAS == 1 ? 216 : 110) * 1024) / STAGE_BYTES);
   static constexpr int STAGES = STAGES_FIT > 8 ? 8 : (STAGES_FIT < 3 ? 3 : STAGES_FIT);
-  static constexpr int NCONS = 32 * RPT;
-  static constexpr int NTD = NCONS + 32;
   static constexpr int NB = K / 8;      // 8-column blocks of Y
+  // Consumer warp grid WM (row groups) x WN (column groups); a warp owns MB 8-row blocks x NBW 8-column blocks of Y.
+  // Default: one 16-row slab x all columns per warp (WM = RPT).  A warp runs on sub-partition (warp id % 4) of the SM,
+  // and each sub-partition has its own fp64 tensor pipe: the 14 slab warps of the 224-row CTA land 4 / 4 / 3 / 3 on
+  // the four pipes, so the kernel cannot pass 87.5 % of the DMMA peak (measured: 84 % busy, r02c_ncu_dense_tiled.txt).
+  // The 224-row CTA therefore uses 4 x 2 warps of 56 rows x K / 2 columns: two consumer warps on every pipe.
+  static constexpr bool GRID8 = (RPT == 14 && NB >= 2);
+  static constexpr int WM = GRID8 ? 4 : RPT;
+  static constexpr int WN = GRID8 ? 2 : 1;
+  static constexpr int MB = TR / 8 / WM;
+  static constexpr int NBW = NB / WN;
+  static constexpr int NCONS = 32 * WM * WN;
+  static constexpr int NTD = NCONS + 32;
+  static_assert(MB * WM * 8 == TR && NBW * WN == NB, "warp grid must tile the CTA's block of Y");
   static_assert(TRP % 16 == 4 && (KP % 16 == 4 || KP % 16 == 12), "row strides must spread the four k-rows over the bank pairs");
   static constexpr size_t SMEM_BYTES = STAGE_BYTES * STAGES;
 };
@@ -190,7 +201,7 @@ template <int K, int RPT, bool TILED>
 __global__ void __launch_bounds__(DmmaTiling<K, RPT>::NTD, DmmaTiling<K, RPT>::CTAS)
     k_dense_dmma(int n, int npad, const double* __restrict__ A, int64_t ld, const double* __restrict__ X, double* __restrict__ Y) {
   using D = DmmaTiling<K, RPT>;
-  constexpr int TR = D::TR, KC = D::KC, STAGES = D::STAGES, NB = D::NB, TRP = D::TRP, KP = D::KP;
+  constexpr int TR = D::TR, KC = D::KC, STAGES = D::STAGES, TRP = D::TRP, KP = D::KP;
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ uint64_t bar_full[STAGES], bar_empty[STAGES];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -217,7 +228,7 @@ __global__ void __launch_bounds__(DmmaTiling<K, RPT>::NTD, DmmaTiling<K, RPT>::C
   const int c0 = blockIdx.y * per_split;
   const int nchunks = max(0, min(npad / KC, c0 + per_split) - c0);
   Y += (size_t)blockIdx.y * (size_t)n * K;
-  if (warp == RPT) {  // ---- producer warp: KC slices of A (one per column, contiguous by symmetry) + KC rows of X
+  if (warp == D::NCONS / 32) {  // ---- producer warp: KC slices of A (one per column, contiguous by symmetry) + KC rows of X
     const uint32_t a_line = (uint32_t)(rows * sizeof(double));
     constexpr uint32_t x_line = (uint32_t)(K * sizeof(double));
     for (int ci = 0; ci < nchunks; ++ci) {
@@ -245,14 +256,16 @@ __global__ void __launch_bounds__(DmmaTiling<K, RPT>::NTD, DmmaTiling<K, RPT>::C
     }
     return;
   }
-  // ---- consumer warps: rows [warp*16, warp*16 + 16) of the tile
+  // ---- consumer warps: MB 8-row blocks from row rbase of the tile x NBW 8-column blocks from column block cb0
+  constexpr int MB = D::MB, NBW = D::NBW;
   const int g = lane >> 2, t = lane & 3;
-  const bool active = warp * 16 < rows;  // the last tile may hold fewer slabs (their smem rows are stale: never stored)
-  double acc[2][NB][2];
+  const int rbase = (warp % D::WM) * (MB * 8), cb0 = (warp / D::WM) * NBW;
+  const bool active = rbase < rows;  // the last tile may hold fewer rows (stale smem rows are computed on but never stored)
+  double acc[MB][NBW][2];
 #pragma unroll
-  for (int mb = 0; mb < 2; ++mb)
+  for (int mb = 0; mb < MB; ++mb)
 #pragma unroll
-    for (int nb = 0; nb < NB; ++nb) acc[mb][nb][0] = acc[mb][nb][1] = 0.0;
+    for (int nb = 0; nb < NBW; ++nb) acc[mb][nb][0] = acc[mb][nb][1] = 0.0;
   for (int ci = 0; ci < nchunks; ++ci) {
     const int s = ci % STAGES;
     mbar_wait(&bar_full[s], (uint32_t)((ci / STAGES) & 1));
@@ -261,15 +274,15 @@ __global__ void __launch_bounds__(DmmaTiling<K, RPT>::NTD, DmmaTiling<K, RPT>::C
     if (active) {
 #pragma unroll
       for (int k0 = 0; k0 < KC; k0 += 4) {
-        double a[2], b[NB];
+        double a[MB], b[NBW];
 #pragma unroll
-        for (int mb = 0; mb < 2; ++mb) a[mb] = As[(k0 + t) * TRP + warp * 16 + mb * 8 + g];
+        for (int mb = 0; mb < MB; ++mb) a[mb] = As[(k0 + t) * TRP + rbase + mb * 8 + g];
 #pragma unroll
-        for (int nb = 0; nb < NB; ++nb) b[nb] = Xs[(k0 + t) * KP + nb * 8 + g];
+        for (int nb = 0; nb < NBW; ++nb) b[nb] = Xs[(k0 + t) * KP + (cb0 + nb) * 8 + g];
 #pragma unroll
-        for (int mb = 0; mb < 2; ++mb)
+        for (int mb = 0; mb < MB; ++mb)
 #pragma unroll
-          for (int nb = 0; nb < NB; ++nb) dmma_884(acc[mb][nb], a[mb], b[nb]);
+          for (int nb = 0; nb < NBW; ++nb) dmma_884(acc[mb][nb], a[mb], b[nb]);
       }
     }
     __syncwarp();
@@ -277,15 +290,15 @@ __global__ void __launch_bounds__(DmmaTiling<K, RPT>::NTD, DmmaTiling<K, RPT>::C
   }
   if (active) {
 #pragma unroll
-    for (int mb = 0; mb < 2; ++mb) {
-      const int r = row0 + warp * 16 + mb * 8 + g;
+    for (int mb = 0; mb < MB; ++mb) {
+      const int r = row0 + rbase + mb * 8 + g;
       if (r >= n) continue;
 #pragma unroll
-      for (int nb = 0; nb < NB; ++nb) {
+      for (int nb = 0; nb < NBW; ++nb) {
         Pack<double, 2> o;
         o.v[0] = acc[mb][nb][0];
         o.v[1] = acc[mb][nb][1];
-        *reinterpret_cast<Pack<double, 2>*>(Y + (size_t)r * K + nb * 8 + 2 * t) = o;
+        *reinterpret_cast<Pack<double, 2>*>(Y + (size_t)r * K + (cb0 + nb) * 8 + 2 * t) = o;
       }
     }
   }
