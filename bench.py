@@ -472,7 +472,7 @@ def run_side_configs(args, peak_hbm: float) -> dict:
 	from scripts import run_configs as rc
 
 	out = {}
-	a = types.SimpleNamespace(c3_scale=args.c3_scale, c3_probes=64, c3_block=64, c3_reorder="balance", c4_n=32768, c5_grid=256, c5_small=48)
+	a = types.SimpleNamespace(c3_scale=args.c3_scale, c3_probes=64, c3_block=64, c3_reorder="balance", c4_n=32768, c4_block=64, c5_grid=256, c5_small=48)
 
 	def guarded(name, fn):
 		t0 = time.perf_counter()
@@ -505,7 +505,7 @@ def run_side_configs(args, peak_hbm: float) -> dict:
 		n = r["n"]
 		flops = 2.0 * n * n  # per probe-step: the dense product dominates (re-orthogonalisation: 4 n j flops at step j)
 		A = torch.randn((n, n), device="cuda", dtype=torch.float64)
-		X = torch.randn((n, 32), device="cuda", dtype=torch.float64)
+		X = torch.randn((n, a.c4_block), device="cuda", dtype=torch.float64)
 		for _ in range(2):
 			torch.matmul(A, X)
 		e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -514,12 +514,12 @@ def run_side_configs(args, peak_hbm: float) -> dict:
 			torch.matmul(A, X)
 		e1.record()
 		torch.cuda.synchronize()
-		dgemm_tf = 5 * 2.0 * n * n * 32 / (e0.elapsed_time(e1) * 1e-3) / 1e12
+		dgemm_tf = 5 * 2.0 * n * n * a.c4_block / (e0.elapsed_time(e1) * 1e-3) / 1e12
 		del A, X
 		ach = flops * r["probe_steps_per_s"] / 1e12
-		return {"workload": f"C4: numerical rank, dense Gram {n}x{n} (rank {r['rank']}), smoothstep, deg=100, orth=100, 64 probes, fp64 (full size)",
+		return {"workload": f"C4: numerical rank, dense Gram {n}x{n} (rank {r['rank']}), smoothstep, deg=100, orth=100, 64 probes in blocks of {a.c4_block}, fp64 (full size)",
 		        "probe_steps_per_s": r["probe_steps_per_s"], "ok": r["ok"], "rank_estimate": r["mean"],
-		        "roofline": {"bound": "fp64 tensor (yardstick: cuBLAS DGEMM n x n x 32 timed in this run)", "achieved": ach, "peak": dgemm_tf,
+		        "roofline": {"bound": f"fp64 tensor (yardstick: cuBLAS DGEMM n x n x {a.c4_block} timed in this run)", "achieved": ach, "peak": dgemm_tf,
 		                     "unit": "TFLOP/s", "frac": ach / dgemm_tf}}  # fmt: skip
 
 	def c5():

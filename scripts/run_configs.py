@@ -219,11 +219,11 @@ def c4(args):
 	lam = ritz_max(op, np.float64)
 	M = MatrixFunction(op, "smoothstep", deg=100, orth=100, a=1e-6 * lam, b=1e-3 * lam)
 	probes = 64
-	y, ms, same = slq_run(M, np.float64, probes, 32)
+	y, ms, same = slq_run(M, np.float64, probes, args.c4_block)
 	st = stats(y)
-	out = {"config": "C4", "n": n, "rank": r, "lambda_max_ritz": lam, "probes": probes, "deg": 100, "orth": 100, "ms": ms,
+	out = {"config": "C4", "n": n, "rank": r, "lambda_max_ritz": lam, "probes": probes, "block": args.c4_block, "deg": 100, "orth": 100, "ms": ms,
 	       "probe_steps_per_s": probes * 100 / ms * 1e3, "deterministic": same, **st}  # fmt: skip
-	out["matrix_GBps"] = n * n * 8 * (probes / 32) * 100 / ms / 1e6
+	out["matrix_GBps"] = n * n * 8 * (probes / args.c4_block) * 100 / ms / 1e6
 	out.update(identity_check(op, np.float64))
 	out["rank_z"] = abs(st["mean"] - r) / (st["std"] / np.sqrt(probes))
 	out["ok"] = bool(same and out["quad_identity_vs_xtAx_rel"] < 1e-10 and out["rank_z"] < 5)
@@ -309,6 +309,7 @@ def main():
 	ap.add_argument("--c3-block", type=int, default=64)
 	ap.add_argument("--c3-reorder", default="balance", type=lambda v: False if v in ("0", "none", "False") else v)
 	ap.add_argument("--c4-n", type=int, default=32768)
+	ap.add_argument("--c4-block", type=int, default=32)
 	ap.add_argument("--c5-grid", type=int, default=256)
 	ap.add_argument("--c5-small", type=int, default=96)
 	ap.add_argument("--out", default="gpurun_out/configs.jsonl")
