@@ -46,13 +46,15 @@ struct Workspace {
 
 inline size_t ws_layout(int64_t n, int k, int ncv, int dtype, Workspace* ws, char* base) {
   size_t panel = align_up((size_t)n * k * dtype_size(dtype), 256);
+  // ncv == 2 (orth <= 2): one panel more than the recurrence needs, for the fused step's second output (lanczos_impl)
+  const int np = ncv + (ncv == 2 ? 1 : 0);
   size_t off = 0;
   size_t panels_off = off;
-  off += panel * (size_t)ncv;
+  off += panel * (size_t)np;
   size_t sc_off = off;
   off += align_up(sizeof(LzScal), 256);
   size_t scales_off = off;
-  off += align_up(sizeof(double) * MAXK * (size_t)(ncv + 1), 256);
+  off += align_up(sizeof(double) * MAXK * (size_t)(np + 1), 256);
   size_t partial_off = off;
   int sms = sm_count();
   if (sms <= 0) sms = 148;
@@ -60,7 +62,7 @@ inline size_t ws_layout(int64_t n, int k, int ncv, int dtype, Workspace* ws, cha
   if (ws) {
     ws->base = base + panels_off;
     ws->panel_bytes = panel;
-    ws->npanel = ncv;
+    ws->npanel = np;
     ws->sc = reinterpret_cast<LzScal*>(base + sc_off);
     ws->scales = reinterpret_cast<double*>(base + scales_off);
     ws->partial = reinterpret_cast<double*>(base + partial_off);

@@ -15,6 +15,7 @@
 // in fixed order by the last CTA to finish, which also runs the scalar recurrence bookkeeping (early break
 // mask, lanczos.h:140).  Dots and norms accumulate in fp64 for both fp32 and fp64 panels.
 #include <cooperative_groups.h>
+#include <type_traits>
 
 #include <cmath>
 #include <cstdlib>
@@ -65,14 +66,14 @@ __device__ __forceinline__ double round_to(double x) {
 }
 
 // ---- finalisers (run by every thread of the last CTA) ---------------------------------------------------
-enum Fin { FIN_INIT = 0, FIN_ALPHA = 1, FIN_BETA = 2, FIN_COEF = 3 };
+enum Fin { FIN_INIT = 0, FIN_ALPHA = 1, FIN_BETA = 2, FIN_COEF = 3, FIN_FUSED = 4 };
 
 template <typename T, int K, int FIN>
 __device__ __forceinline__ void finalize(const double* partial, LzScal* sc, double* scale_a, const double* scale_b,
                                          const StepOut& so, double* smem) {
-  constexpr int NACC = (FIN == FIN_COEF) ? 2 : 1;
+  constexpr int NACC = (FIN == FIN_COEF) ? 2 : (FIN == FIN_FUSED ? 3 : 1);
   constexpr int NS = NACC * K;
-  __shared__ double s_res[2 * MAXK];
+  __shared__ double s_res[3 * MAXK];
   reduce_partials<NS>(partial, gridDim.x, smem, s_res);
   const int t = threadIdx.x;
   if (t < K) {
@@ -102,6 +103,40 @@ __device__ __forceinline__ void finalize(const double* partial, LzScal* sc, doub
       sc->beta[t] = b;
       scale_a[t] = round_to<T>(1.0 / b);
       sc->coef[t] = 0.0;
+    } else if (FIN == FIN_FUSED) {
+      // Fused step (k_stepA_tma<STEP_FUSED>): alpha_j = <q_c, w> AND a provisional beta_{j+1} = ||w - alpha_j q_c|| in one
+      // finaliser, the norm from the three sums the step kernel accumulated in fp64 -- S_a = <q_c, w>, S_w = <w, w>,
+      // S_v = <v_c, v_c> -- so that the vector v_n = w - cf v_c need not exist before the next step starts (it is
+      // formed on the fly there):   ||v_n||^2 = S_w - 2 cf <v_c, w> + cf^2 S_v,  <v_c, w> = S_a / r_c,  cf = alpha_j r_c.
+      // The subtraction loses log10(S_w / ||v_n||^2) of the 16 digits carried, so the provisional value only SCALES the
+      // next vector (vectors are stored un-normalised: a scale off by 1e-15 is a normalisation rounding error).  What
+      // is RECORDED as beta_j, and what the early-break test of lanczos.h:139-143 looks at, is the exact norm
+      // sqrt(S_v) of the formed vector, which arrives one step later (here, for the current vector): a breakdown is
+      // therefore noticed one kernel late and the step that should not have run is simply not recorded.
+      const double r = scale_b[t];
+      bool act = sc->active[t] != 0;
+      if (act && so.j > 0) {
+        const double bex = round_to<T>(sqrt(s_res[2 * K + t]));
+        reinterpret_cast<T*>(so.beta)[(size_t)t * so.ld + so.j] = (T)bex;
+        if (bex < so.tol) {  // the reference stopped after the previous step: steps stays j
+          act = false;
+          sc->active[t] = 0;
+        }
+      }
+      const double a = round_to<T>(s_res[t]);
+      const double cf = round_to<T>(a * r);
+      sc->coef[t] = cf;
+      const double vw = (r != 0.0) ? s_res[t] / r : 0.0;
+      const double b2 = s_res[K + t] - 2.0 * cf * vw + cf * cf * s_res[2 * K + t];
+      const double b = round_to<T>(sqrt(fmax(b2, 0.0)));
+      if (act) {
+        reinterpret_cast<T*>(so.alpha)[(size_t)t * so.ld + so.j] = (T)a;
+        reinterpret_cast<T*>(so.beta)[(size_t)t * so.ld + so.j + 1] = (T)b;  // provisional (final only for j + 1 == deg)
+        sc->steps[t] = so.j + 1;
+        if (so.j + 1 == so.deg) sc->active[t] = 0;
+      }
+      sc->beta[t] = b;
+      scale_a[t] = (b > 0.0) ? round_to<T>(1.0 / b) : 0.0;
     } else {  // FIN_COEF: one modified-Gram-Schmidt projection coefficient (lanczos.h:59-64)
       double r = scale_b[t];
       double u_norm = round_to<T>(s_res[t] * r * r);
@@ -307,14 +342,18 @@ __device__ __forceinline__ void chunk_gather(T (&acc)[V], const RowChunk<T, CsrT
 
 // PLAIN: w = A u_c only (slq_op_matmat).  REPLAY: the whole Lanczos step with RECORDED alpha/beta (second pass of the
 // basis-free f(A) X): v = (A u_c) r_c - beta r_p u_p - alpha r_c u_c and Y += c_{j+1} ||x|| r_n v in one kernel.
-enum StepMode { STEP_FIRST = 0, STEP_NEXT = 1, STEP_PLAIN = 2, STEP_REPLAY = 3 };
+// FUSED (bulk-copy kernel, rows of <= 64 non-zeros, orth = 0): one kernel per Lanczos step.  The update v = w - cf u of the
+// PREVIOUS step is applied on the fly (own rows: written out; gathered neighbours: recomputed from the two staged tiles)
+// and the step's norm comes out of the finaliser (FIN_FUSED), so the separate k_axpy pass over three panels goes away.
+enum StepMode { STEP_FIRST = 0, STEP_NEXT = 1, STEP_PLAIN = 2, STEP_REPLAY = 3, STEP_FUSED = 4 };
 
 // Per-step scalars of the replay (one row of the table built by k_replay_table): rc | brp | cf | yc, MAXK doubles each.
 struct ReplayArgs {
   const double* row = nullptr;
   const double* y0 = nullptr;  // coefficient of the start vector (read when first != 0)
-  void* Y = nullptr;           // n x K accumulator panel
+  void* Y = nullptr;           // n x K accumulator panel (STEP_FUSED: the panel the formed vector is written to, or NULL)
   int first = 0;
+  double* scale_out = nullptr;  // STEP_FUSED: where the finaliser stores the scale 1 / beta of the NEXT vector
 };
 
 // ---- kernel A (CSR operators): w = (A u_c) r_c - beta_j (u_p r_p); alpha partials ------------------------------------
@@ -453,6 +492,16 @@ static bool use_tma_path() {
   if (cached < 0) {
     const char* e = getenv("SLQ_STEPA");
     cached = (e && strcmp(e, "csr") == 0) ? 0 : 1;
+  }
+  return cached == 1;
+}
+
+// SLQ_FUSED=0 keeps the two-kernel step (step A + axpy) everywhere (A/B timing, parity of the two paths).
+static bool use_fused_step() {
+  static int cached = -1;
+  if (cached < 0) {
+    const char* e = getenv("SLQ_FUSED");
+    cached = (e && strcmp(e, "0") == 0) ? 0 : 1;
   }
   return cached == 1;
 }
@@ -934,6 +983,47 @@ static int lanczos_impl(slq_op* op, T* X, int deg, double rtol, int orth, int nc
 
   k_init<T, K><<<g_vec, NT, 0, st>>>(n, X, ws.sc, scale_of(0), ws.partial, so);
   SLQ_LAUNCH_CHECK();
+
+  // ---- fused path (orth = 0, CSR rows of <= 64 non-zeros, no basis wanted): ONE kernel per step -------------------------
+  // Panels: the pending w of the previous step, its vector u, and this step's two outputs (the formed vector, the new w):
+  // the caller's X plus three workspace panels (ws_layout reserves the third when ncv == 2).  Scales rotate through
+  // three rows of ws.scales: row j % 3 belongs to vector j.
+  if constexpr (tma_supported<T, K>()) {
+    const bool aligned = (((uintptr_t)op->colidx | (uintptr_t)op->vals | (uintptr_t)X | (uintptr_t)ws.base) & 15) == 0;
+    if (orth == 0 && !Qout && op->kind == OP_CSR && op->max_row_nnz <= TmaTiling<T, K>::LONG && ws.npanel >= 3 && aligned &&
+        use_tma_path() && use_fused_step()) {
+      T* P[4] = {X, reinterpret_cast<T*>(ws.base), reinterpret_cast<T*>(ws.base + ws.panel_bytes),
+                 reinterpret_cast<T*>(ws.base + 2 * ws.panel_bytes)};
+      std::vector<int> freep = {3, 2, 1};
+      int iW = 0, iU = 0;  // first step: "pending w" = the start block with cf = 0 (k_init), u = the start block
+      for (int j = 0; j < deg; ++j) {
+        so.j = j;
+        const int iWn = freep.back();
+        freep.pop_back();
+        int iV = -1;
+        if (j > 0) {
+          iV = freep.back();
+          freep.pop_back();
+        }
+        const int pslot = prof_begin(PROF_STEPA, st);
+        int rc = launch_stepA_fused<T, K>(op, P[iW], P[iU], P[iWn], iV >= 0 ? P[iV] : nullptr, ws.sc, scale_of(j % 3), scale_of((j + 2) % 3),
+                                          scale_of((j + 1) % 3), ws.partial, so, st);
+        if (rc != SLQ_OK) return rc;
+        prof_end(PROF_STEPA, pslot, st);
+        if (j > 0) {
+          freep.push_back(iW);
+          freep.push_back(iU);
+          iU = iV;
+        }
+        iW = iWn;
+      }
+      if (steps || xnorm2) {
+        k_copy_steps<<<1, MAXK, 0, st>>>(ws.sc, K, steps, xnorm2);
+        SLQ_LAUNCH_CHECK();
+      }
+      return SLQ_OK;
+    }
+  }
 
   int pos[3] = {ncv - 1, 0, 1 % ncv};
   int F = free_list.back();

@@ -73,6 +73,12 @@ __device__ __forceinline__ void cp_async_wait() {
 #ifndef SLQ_TMA_R
 #define SLQ_TMA_R 2  // rows per thread processed together
 #endif
+#ifndef SLQ_TMA_RF
+#define SLQ_TMA_RF 1
+#endif
+#ifndef SLQ_TMA_RF512
+#define SLQ_TMA_RF512 1
+#endif
 #ifndef SLQ_TMA_PREFETCH
 #define SLQ_TMA_PREFETCH 0  // 1: the producer warp also prefetches the off-tile probe rows of the last issued stage into L2
 #endif
@@ -81,12 +87,17 @@ __device__ __forceinline__ void cp_async_wait() {
 #endif
 
 // BAL: layout of the non-zero-balanced variant (irregular operators): larger index chunks, fewer stages, row sums in smem.
-template <typename T, int K, bool BAL = false>
+#ifndef SLQ_TMA_CWF
+#define SLQ_TMA_CWF 15  // consumer warps of the fused step at 512-byte rows (fp64, k = 64); 10 warps x 2 rows in flight measured -6%
+#endif
+template <typename T, int K, bool BAL = false, bool FUSEDT = false>
 struct TmaTiling {
   // consumer warps (+1 producer).  Lean: 15 (512 threads, 128 registers each, one CTA per SM).  Balanced: 11 (384
   // threads) and TWO CTAs per SM -- its consumers meet at two CTA barriers per chunk (the slice hand-over of rows that
   // span slices), and a second, independent CTA fills the issue slots the first one leaves idle while it waits there.
-  static constexpr int CW = BAL ? 11 : 15;
+  // (Tuning knob of the fused step at 512-byte rows: fewer warps with more registers each, so that a thread keeps two
+  // rows' gathers in flight.  Measured slower than 15 warps x 1 row: the shared-memory pipe, 71 % busy, is the limit.)
+  static constexpr int CW = BAL ? 11 : ((FUSEDT && K * (int)sizeof(T) == 512) ? SLQ_TMA_CWF : 15);
   static constexpr int CTAS_PER_SM = BAL ? 2 : 1;
   static constexpr int CT = CW * 32;                   // consumer threads
   static constexpr int NTHREADS = CT + 32;             // + producer warp
@@ -98,6 +109,8 @@ struct TmaTiling {
   static constexpr int TILE = BAL ? 4 * RPP : (TILE_MAX < 120 ? TILE_MAX : 120);
   static constexpr int PASSES = TILE / RPP;
   static constexpr int R = PASSES % SLQ_TMA_R == 0 ? SLQ_TMA_R : 1;  // rows per thread processed together
+  static constexpr int RFW = (FUSEDT && K * (int)sizeof(T) == 512) ? SLQ_TMA_RF512 : SLQ_TMA_RF;
+  static constexpr int RF = PASSES % RFW == 0 ? RFW : 1;  // ... in the fused step (two loads per non-zero)
   static constexpr size_t PANEL = (size_t)TILE * K * sizeof(T);
   // Balanced variant (irregular operators): no staged u_c / u_p tiles (on a power-law graph next to no column is
   // tile-local); the shared memory goes to a ring of RING 16-byte slots PER CONSUMER THREAD instead, filled by
@@ -191,19 +204,77 @@ __device__ __forceinline__ void tma_gather_rows(T (&acc)[R][V], const int (&s)[R
   }
 }
 
+// Fused step: the gathered vector does not exist yet -- entry (c, slot) of it is w[c] - cf u[c], formed from the two
+// staged tiles (in-tile columns) or two global rows, in exactly the arithmetic the row's owner uses when it writes the
+// vector out (fnma_rn), so every CTA sees the same values.  Both loads of all R x U non-zeros are issued before use.
+#ifndef SLQ_TMA_UF
+#define SLQ_TMA_UF 5  // gathers (pairs of loads) per row per round, fused step
+#endif
+template <typename T, int K, int V, int U, int R, int TILE>
+__device__ __forceinline__ void tma_gather_rows_fused(T (&acc)[R][V], const int (&s)[R], const int (&e)[R], const int* __restrict__ ci,
+                                                      const T* __restrict__ va, const T* s_w, const T* s_u, int row0,
+                                                      const T* __restrict__ W, const T* __restrict__ Uv, int slot, const T (&cf)[V]) {
+  // Branch-free: an in-tile column and an off-tile one differ only in the (generic) address the two rows are loaded
+  // from -- the staged tiles or the global panels, each pair a constant distance apart -- and a slot past the end of a
+  // short row re-reads entry 0 of the stage with a zero matrix value (fma(0, x, acc) == acc).  The per-non-zero
+  // branches of the first version cost more issue slots than the loads and FMAs together (profiles/r02d_fused_step.md).
+  const ptrdiff_t d_smem = s_u - s_w, d_glob = Uv - W;
+  int len = 0, lmin = 0x7fffffff;
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    len = max(len, e[r] - s[r]);
+    lmin = min(lmin, e[r] - s[r]);
+  }
+  auto round = [&](int i, auto ragged) {
+    constexpr bool RAGGED = decltype(ragged)::value;
+    Pack<T, V> wv[R][U], uv[R][U];
+    T a[R][U];
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        int idx = s[r] + i + u;
+        bool ok = true;
+        if (RAGGED) {
+          ok = idx < e[r];
+          idx = ok ? idx : 0;
+        }
+        const int c = ci[idx];
+        a[r][u] = ok ? va[idx] : (T)0;
+        const unsigned loc = (unsigned)(c - row0);
+        const bool in = loc < (unsigned)TILE;
+        const T* pw = in ? s_w + (size_t)loc * K + slot : W + (size_t)c * K + slot;
+        const T* pu = pw + (in ? d_smem : d_glob);
+        wv[r][u] = *reinterpret_cast<const Pack<T, V>*>(pw);
+        uv[r][u] = *reinterpret_cast<const Pack<T, V>*>(pu);
+      }
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+#pragma unroll
+        for (int q = 0; q < V; ++q) acc[r][q] = fma(a[r][u], fnma_rn(cf[q], uv[r][u].v[q], wv[r][u].v[q]), acc[r][q]);
+  };
+  int i = 0;
+  for (; i + U <= lmin; i += U) round(i, std::false_type{});
+  for (; i < len; i += U) round(i, std::true_type{});
+}
+
 // LONGROWS = false: compiled without the shared long-row path (operators whose longest row has <= LONG non-zeros; the
 // extra live state costs the lean kernel registers -- it spilled and ran 2.4x slower with the path compiled in).
 template <typename T, int K, int MODE, bool LONGROWS>
-__global__ void __launch_bounds__(TmaTiling<T, K, LONGROWS>::NTHREADS, TmaTiling<T, K, LONGROWS>::CTAS_PER_SM)
+__global__ void __launch_bounds__(TmaTiling<T, K, LONGROWS, MODE == STEP_FUSED>::NTHREADS, TmaTiling<T, K, LONGROWS, MODE == STEP_FUSED>::CTAS_PER_SM)
     k_stepA_tma(int n, const int32_t* __restrict__ rowptr, const int32_t* __restrict__ colidx, const T* __restrict__ vals,
                 const T* __restrict__ uc, const T* __restrict__ up, T* __restrict__ w, LzScal* sc, const double* scale_c,
                 const double* scale_p, double* partial, StepOut so, ReplayArgs rp) {
-  using C = TmaTiling<T, K, LONGROWS>;
+  using C = TmaTiling<T, K, LONGROWS, MODE == STEP_FUSED>;
   constexpr int V = C::V, LPR = C::LPR, RPP = C::RPP, PASSES = C::PASSES, TILE = C::TILE, CAP = C::CAP;
   constexpr int STAGES = LONGROWS ? C::BAL_STAGES : C::STAGES;  // the balanced variant gives stages up for the row accumulators
   constexpr int UB = SLQ_TMA_UB;
-  constexpr int U = SLQ_TMA_U, R = C::R;
+  constexpr int U = SLQ_TMA_U, R = (MODE == STEP_FUSED) ? C::RF : C::R;
   constexpr bool FIRST = (MODE == STEP_FIRST), PLAIN = (MODE == STEP_PLAIN), REPLAY = (MODE == STEP_REPLAY);
+  constexpr bool FUSED = (MODE == STEP_FUSED);  // uc = the pending w of the previous step, up = its vector u (see StepMode)
+  static_assert(!(FUSED && LONGROWS), "the fused step exists for the lean variant only");
   constexpr bool HAS_UP = !FIRST && !PLAIN;
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ uint64_t bar_full[STAGES], bar_empty[STAGES];
@@ -213,7 +284,7 @@ __global__ void __launch_bounds__(TmaTiling<T, K, LONGROWS>::NTHREADS, TmaTiling
   double* s_red = reinterpret_cast<double*>(s_scratch);  // alpha partials per consumer warp; re-used by the finaliser
   T* s_part = reinterpret_cast<T*>(s_scratch);           // long rows: one partial probe-row per row group
   __shared__ T s_rc[K], s_brp[K];
-  __shared__ T s_cf[REPLAY ? K : 1], s_yc[REPLAY ? K : 1], s_y0[REPLAY ? K : 1];  // replay: alpha_j r_c, Y coefficients
+  __shared__ T s_cf[(REPLAY || FUSED) ? K : 1], s_yc[REPLAY ? K : 1], s_y0[REPLAY ? K : 1];  // alpha r_c (replay: of this step; fused: of the previous one), Y coefficients
 
   unsigned char* const base = smem_raw;  // bulk copies need 16-byte alignment only
   T* const s_acc = reinterpret_cast<T*>(smem_raw + (size_t)STAGES * C::STAGE_BYTES);  // balanced variant: TILE x K row sums
@@ -245,14 +316,17 @@ __global__ void __launch_bounds__(TmaTiling<T, K, LONGROWS>::NTHREADS, TmaTiling
     for (int t = tid; t < K; t += C::NTHREADS) {
       s_rc[t] = (T)scale_c[t];
       s_brp[t] = FIRST ? (T)0 : (T)(sc->beta[t]) * (T)scale_p[t];
+      if (FUSED) s_cf[FUSED ? t : 0] = (T)sc->coef[t];  // pending update of the previous step (0 at the first)
     }
   }
   __syncthreads();
 
   const int ntiles = (n + TILE - 1) / TILE;
-  double acc_a[V];
+  double acc_a[V], acc_w[FUSED ? V : 1], acc_v[FUSED ? V : 1];  // <q_c, w>; fused: <w, w>, <v_c, v_c>
 #pragma unroll
   for (int q = 0; q < V; ++q) acc_a[q] = 0.0;
+#pragma unroll
+  for (int q = 0; q < (FUSED ? V : 1); ++q) acc_w[q] = acc_v[q] = 0.0;
 
   if (warp == C::CW) {
     // ------------------------------------------------ producer warp ------------------------------------------------
@@ -323,7 +397,8 @@ __global__ void __launch_bounds__(TmaTiling<T, K, LONGROWS>::NTHREADS, TmaTiling
         __syncwarp();
         if (lane == 0) {
           const uint32_t b_ci = (uint32_t)nb * 4u, b_va = (uint32_t)nb * (uint32_t)sizeof(T);
-          const uint32_t b_up = (!LONGROWS && HAS_UP && last) ? (uint32_t)nrows * K * (uint32_t)sizeof(T) : 0u;
+          // (fused: in-tile columns are formed from BOTH tiles, so u_p travels with every chunk like u_c)
+          const uint32_t b_up = (!LONGROWS && HAS_UP && (last || FUSED)) ? (uint32_t)nrows * K * (uint32_t)sizeof(T) : 0u;
           const uint32_t b_uc = LONGROWS ? 0u : (uint32_t)nrows * K * (uint32_t)sizeof(T);  // every chunk: in-tile columns read it
           const uint32_t total = b_ci + b_va + b_up + b_uc;
           if (total > 0) {
@@ -360,11 +435,12 @@ __global__ void __launch_bounds__(TmaTiling<T, K, LONGROWS>::NTHREADS, TmaTiling
     // this thread's probe columns never change: keep their scales in registers (the per-row shared-memory reads were
     // a fifth of the kernel's L1/shared-memory wavefronts, and that pipe is the co-bottleneck next to HBM)
     constexpr int HOIST = sizeof(T) == 8 ? SLQ_TMA_HOIST : 0;  // the fp32 k = 64 variant has no registers to spare
-    T rc_r[V], brp_r[V];
+    T rc_r[V], brp_r[V], cf_r[V];
 #pragma unroll
     for (int q = 0; q < V; ++q) {
       rc_r[q] = (PLAIN || REPLAY || HOIST < 2) ? (T)1 : s_rc[slot + q];
       brp_r[q] = (PLAIN || REPLAY || HOIST < 1) ? (T)0 : s_brp[slot + q];
+      cf_r[q] = FUSED ? s_cf[FUSED ? slot + q : 0] : (T)0;
     }
     if constexpr (!LONGROWS) {
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
@@ -411,11 +487,40 @@ __global__ void __launch_bounds__(TmaTiling<T, K, LONGROWS>::NTHREADS, TmaTiling
               }
             }
           }
-          tma_gather_rows<T, K, V, U, R, TILE>(a2, s, e, s_ci, s_va, s_uc, row0, uc, slot);
+          if constexpr (FUSED)
+            tma_gather_rows_fused<T, K, V, SLQ_TMA_UF, R, TILE>(a2, s, e, s_ci, s_va, s_uc, s_up, row0, uc, up, slot, cf_r);
+          else
+            tma_gather_rows<T, K, V, U, R, TILE>(a2, s, e, s_ci, s_va, s_uc, row0, uc, slot);
 #pragma unroll
           for (int r = 0; r < R; ++r)
 #pragma unroll
             for (int q = 0; q < V; ++q) acc[g * R + r][q] = a2[r][q];
+          if constexpr (FUSED) {
+            if (last) {
+#pragma unroll
+              for (int r = 0; r < R; ++r) {
+                const int rl = (g * R + r) * RPP + rloc;
+                if (row0 + rl < n) {
+                  const size_t off = (size_t)(row0 + rl) * K + slot;
+                  const Pack<T, V> pw = *reinterpret_cast<const Pack<T, V>*>(s_uc + (size_t)rl * K + slot);  // pending w of the previous step
+                  const Pack<T, V> pu = *reinterpret_cast<const Pack<T, V>*>(s_up + (size_t)rl * K + slot);  // its vector u
+                  Pack<T, V> vn, wv;
+#pragma unroll
+                  for (int q = 0; q < V; ++q) {
+                    const T rcq = HOIST >= 2 ? rc_r[q] : s_rc[slot + q];
+                    const T brq = HOIST >= 1 ? brp_r[q] : s_brp[slot + q];
+                    vn.v[q] = fnma_rn(cf_r[q], pu.v[q], pw.v[q]);                      // the current vector, formed at last
+                    wv.v[q] = fnma_rn(brq, pu.v[q], mul_rn(a2[r][q], rcq));            // w = (A v) r_c - beta r_p u
+                    acc_a[q] += (double)(vn.v[q] * rcq) * (double)wv.v[q];
+                    acc_w[FUSED ? q : 0] += (double)wv.v[q] * (double)wv.v[q];
+                    acc_v[FUSED ? q : 0] += (double)vn.v[q] * (double)vn.v[q];
+                  }
+                  if (rp.Y) st_pack<T, V, false>(reinterpret_cast<T*>(rp.Y) + off, vn);
+                  st_pack<T, V, false>(w + off, wv);
+                }
+              }
+            }
+          } else
           if (last) {
 #pragma unroll
             for (int r = 0; r < R; ++r) {
@@ -660,6 +765,30 @@ __global__ void __launch_bounds__(TmaTiling<T, K, LONGROWS>::NTHREADS, TmaTiling
     }
   }
 
+  if constexpr (FUSED) {
+    // three sums per probe column, reduced one after the other through the same scratch: partial[cta][which][column]
+#pragma unroll
+    for (int which = 0; which < 3; ++which) {
+      if (warp < C::CW) {
+#pragma unroll
+        for (int q = 0; q < V; ++q) {
+          double x = which == 0 ? acc_a[q] : (which == 1 ? acc_w[FUSED ? q : 0] : acc_v[FUSED ? q : 0]);
+#pragma unroll
+          for (int off = 16; off >= LPR; off >>= 1) x += __shfl_xor_sync(0xffffffffu, x, off);
+          if (lane < LPR) s_red[warp * K + lane * V + q] = x;
+        }
+      }
+      __syncthreads();
+      if (tid < K) {
+        double sum = 0.0;
+#pragma unroll
+        for (int wi = 0; wi < C::CW; ++wi) sum += s_red[wi * K + tid];
+        partial[((size_t)blockIdx.x * 3 + which) * K + tid] = sum;
+      }
+      __syncthreads();
+    }
+    if (elect_last_cta(&sc->counter)) finalize<T, K, FIN_FUSED>(partial, sc, rp.scale_out, scale_c, so, s_red);
+  } else
   if (!PLAIN && !REPLAY) {
     // deterministic CTA reduction of the alpha partials: row groups inside a warp by shuffles, warps through shared memory
     if (warp < C::CW) {
@@ -708,6 +837,29 @@ static int launch_stepA_tma(const slq_op* op, const T* uc, const T* up, T* w, Lz
   else
     k_stepA_tma<T, K, MODE, false><<<g, C::NTHREADS, C::SMEM_BYTES, st>>>(n, op->rowptr, op->colidx, (const T*)op->vals, uc, up, w, sc,
                                                                           scale_c, scale_p, partial, so, rp);
+  SLQ_LAUNCH_CHECK();
+  return SLQ_OK;
+}
+
+// Fused step (lean variant only: the caller checks op->max_row_nnz <= LONG).  W / U: pending w and vector u of the previous
+// step (the start block twice at the first step, where cf = 0); w_out, v_out: this step's w and the formed vector.
+template <typename T, int K>
+static int launch_stepA_fused(const slq_op* op, const T* W, const T* U, T* w_out, T* v_out, LzScal* sc, const double* scale_c,
+                              const double* scale_p, double* scale_out, double* partial, const StepOut& so, cudaStream_t st) {
+  using C = TmaTiling<T, K, false, true>;
+  static DeviceOnce once;
+  if (once.needed()) {
+    SLQ_CUDA(cudaFuncSetAttribute(k_stepA_tma<T, K, STEP_FUSED, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM_BYTES));
+    once.done();
+  }
+  const int n = (int)op->n;
+  const int ntiles = (n + C::TILE - 1) / C::TILE;
+  const int g = ntiles < sm_count() ? ntiles : sm_count();
+  ReplayArgs rp;
+  rp.Y = v_out;
+  rp.scale_out = scale_out;
+  k_stepA_tma<T, K, STEP_FUSED, false><<<g, C::NTHREADS, C::SMEM_BYTES, st>>>(n, op->rowptr, op->colidx, (const T*)op->vals, W, U, w_out, sc,
+                                                                              scale_c, scale_p, partial, so, rp);
   SLQ_LAUNCH_CHECK();
   return SLQ_OK;
 }
