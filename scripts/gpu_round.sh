@@ -20,10 +20,10 @@ cat $OUT/bench_ref.json
 SMALL="python bench.py --steps 1 --warmup 3 --probes 64 --no-cpu-baseline --no-e2e --no-configs"
 echo "== ncu launch list"
 $SMALL > $OUT/plain_small.log 2>&1 &&
-timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -s 330 -c 112 --csv --log-file $OUT/launches.csv $SMALL > $OUT/ncu_launches.log 2>&1
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -s 172 -c 58 --csv --log-file $OUT/launches.csv $SMALL > $OUT/ncu_launches.log 2>&1
 echo "ncu launches exit $?"
-echo "== ncu --set full (k_stepA_csr, k_axpy)"
+echo "== ncu --set full (the fused step kernel; k_axpy only exists with SLQ_FUSED=0)"
 $SMALL > $OUT/plain_small2.log 2>&1 &&
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:'k_stepA_tma|k_stepA_csr|k_axpy' -s 310 -c 4 -o $OUT/prof_step $SMALL > $OUT/ncu_full.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:'k_stepA_tma|k_stepA_csr|k_axpy' -s 160 -c 2 -o $OUT/prof_step $SMALL > $OUT/ncu_full.log 2>&1
 echo "ncu full exit $?"
 ls -la $OUT
