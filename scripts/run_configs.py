@@ -137,7 +137,7 @@ def c1(args):
 	B = rng.standard_normal((1000, 1000))
 	A = B @ B.T / 1000 + 0.1 * np.eye(1000)
 	M = MatrixFunction(A, "log", deg=20, orth=0)
-	hutch(M, converge="count", count=32, seed=1)
+	hutch(M, converge="count", count=200, seed=1)
 	t0 = time.perf_counter()
 	est = hutch(M, converge="count", count=200, seed=1)
 	dt = time.perf_counter() - t0

@@ -75,10 +75,19 @@ if os.path.exists(rep):
 					return v * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}[u]
 				tb = tobytes("dram__bytes_read.sum") + tobytes("dram__bytes_write.sum")
 				f.write(f"| **dram traffic (read+write)** | {tb / 1e6:.1f} | MB |\n")
-				key = "k_stepA" if "stepA" in name else ("k_axpy" if "axpy" in name else name)
+				fused = "stepA" in name and ", 4, " in name  # k_stepA_tma<T, K, STEP_FUSED = 4, LONGROWS>
+				key = ("k_stepA_fused" if fused else "k_stepA") if "stepA" in name else ("k_axpy" if "axpy" in name else name)
 				traffic.setdefault(f"{key}_dram_bytes_per_launch", tb)
 			except (KeyError, ValueError):
 				pass
-	with open(os.path.join(dst, "traffic.json"), "w") as f:
-		json.dump(dict(traffic, source=f"profiles/{tag}_ncu_full_summary.md"), f, indent=1)
+	tp = os.path.join(dst, "traffic.json")
+	try:  # keep the entries of kernels this capture did not profile (e.g. the two-kernel step of an earlier round)
+		with open(tp) as f:
+			prev = json.load(f)
+	except (OSError, ValueError):
+		prev = {}
+	prev.update(traffic)
+	prev["source"] = (prev.get("source", "") + f"; profiles/{tag}_ncu_full_summary.md").lstrip("; ")
+	with open(tp, "w") as f:
+		json.dump(prev, f, indent=1)
 print("profiles/ updated from", src)
