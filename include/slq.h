@@ -101,6 +101,14 @@ int slq_dense_create_padded(int64_t n, int64_t npad, const void* A_dev, int64_t 
  * the reduction dimension of Y = A X over several CTAs per row tile (partial slabs of n x k, summed in a fixed order):
  * 16 n k sizeof(T) bytes allow the full split.  Calls that use the scratch must not overlap on different streams. */
 int slq_op_set_scratch(slq_op* op, void* scratch_dev, size_t bytes);
+/* CSR operators, orth = 0, rows of <= 64 non-zeros: slq_lanczos runs ONE kernel per Lanczos step (the update
+ * v = w - alpha q of the previous step is applied on the fly inside the next step's SpMM, DESIGN 3 "fused step") instead
+ * of two (lanczos.h:123-143 as step A + axpy).  It moves 4 panel passes per step instead of 6 but reads TWO rows per
+ * gathered non-zero, so it pays when most non-zeros are local to a row tile of 120 rows (a mesh in the locality order:
+ * +20..30 % on a 2-D 5-point Laplacian) and loses when more than about two non-zeros per row leave the tile (3-D 7-point
+ * Laplacian: -6 %).  enable = 0 keeps the two-kernel step for this operator; the default is 1.  Results agree to
+ * rounding (alpha, beta <= 1e-11 relative; same early-break steps). */
+int slq_op_set_fused_step(slq_op* op, int enable);
 /* Optional band-major copy of an fp64 dense operator for the tensor-core product kernel (the caller owns the buffer; it
  * must outlive the operator or be detached with buf_dev = NULL).  slq_dense_tiled_bytes reports the size (0 when the
  * operator does not take that kernel: fp32, order not a multiple of 16 and not created padded); slq_dense_set_tiled

@@ -38,6 +38,7 @@ _SIGNATURES = {
 	"slq_dense_create": (c_int, [c_int64, c_void_p, c_int64, c_int, POINTER(c_void_p)]),
 	"slq_dense_create_padded": (c_int, [c_int64, c_int64, c_void_p, c_int64, c_int, POINTER(c_void_p)]),
 	"slq_op_set_scratch": (c_int, [c_void_p, c_void_p, c_size_t]),
+	"slq_op_set_fused_step": (c_int, [c_void_p, c_int]),
 	"slq_dense_tiled_bytes": (c_int, [c_void_p, POINTER(c_size_t)]),
 	"slq_dense_set_tiled": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p]),
 	"slq_callback_create": (c_int, [c_int64, c_int, MATMAT_FN, c_void_p, POINTER(c_void_p)]),

@@ -92,6 +92,7 @@ struct slq_op {
   void* scratch;         // optional caller-owned scratch (slq_op_set_scratch): split-K slabs of small dense operators
   size_t scratch_bytes;
   int64_t npad;  // 0, or n rounded up to 16: the array is npad x ld with zero rows / columns past n (slq_dense_create_padded)
+  int no_fused_step;  // 1: keep the two-kernel Lanczos step even where the fused one applies (slq_op_set_fused_step)
   const void* tiled;  // optional band-major copy of the fp64 operator for the tensor-core kernel (slq_dense_set_tiled)
   int tiled_rpt;      // CTA height (16 rpt rows) the copy was laid out for
   // callback

@@ -127,6 +127,12 @@ int slq_dense_create_padded(int64_t n, int64_t npad, const void* A_dev, int64_t 
   return rc;
 }
 
+int slq_op_set_fused_step(slq_op* op, int enable) {
+  SLQ_REQUIRE(op != nullptr, "op is NULL");
+  op->no_fused_step = enable ? 0 : 1;
+  return SLQ_OK;
+}
+
 int slq_op_set_scratch(slq_op* op, void* scratch_dev, size_t bytes) {
   SLQ_REQUIRE(op != nullptr, "op is NULL");
   SLQ_REQUIRE(((uintptr_t)scratch_dev & 31) == 0, "scratch must be 32-byte aligned");

@@ -991,7 +991,7 @@ static int lanczos_impl(slq_op* op, T* X, int deg, double rtol, int orth, int nc
   if constexpr (tma_supported<T, K>()) {
     const bool aligned = (((uintptr_t)op->colidx | (uintptr_t)op->vals | (uintptr_t)X | (uintptr_t)ws.base) & 15) == 0;
     if (orth == 0 && !Qout && op->kind == OP_CSR && op->max_row_nnz <= TmaTiling<T, K>::LONG && ws.npanel >= 3 && aligned &&
-        use_tma_path() && use_fused_step()) {
+        use_tma_path() && use_fused_step() && !op->no_fused_step) {
       T* P[4] = {X, reinterpret_cast<T*>(ws.base), reinterpret_cast<T*>(ws.base + ws.panel_bytes),
                  reinterpret_cast<T*>(ws.base + 2 * ws.panel_bytes)};
       std::vector<int> freep = {3, 2, 1};

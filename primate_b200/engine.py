@@ -60,6 +60,51 @@ def _want_reorder(reorder, n: int, nnz: int) -> bool:
 	return bool(reorder)
 
 
+FUSED_MAX_OFFTILE = 1.75  # off-tile non-zeros per row up to which the one-kernel Lanczos step pays (slq_op_set_fused_step)
+
+
+def _offtile_per_row(indptr: np.ndarray, indices: np.ndarray, tile: int = REORDER_TILE, sample: int = 2000) -> float:
+	"""Non-zeros per row whose column lies outside the row's tile of `tile` consecutive rows, estimated on `sample`
+	evenly spaced tiles (host CSR arrays; a few tens of milliseconds whatever nnz is)."""
+	n = len(indptr) - 1
+	nt = -(-n // tile)
+	if nt == 0:
+		return 0.0
+	off = rows = 0
+	for t in np.unique(np.linspace(0, nt - 1, min(nt, sample)).astype(np.int64)):
+		r0 = int(t) * tile
+		r1 = min(n, r0 + tile)
+		c = indices[indptr[r0] : indptr[r1]]
+		off += int(np.count_nonzero((c < r0) | (c >= r1)))
+		rows += r1 - r0
+	return off / max(rows, 1)
+
+
+def _offtile_per_row_device(rowptr, colidx, n: int, tile: int = REORDER_TILE, sample: int = 2000) -> float:
+	"""`_offtile_per_row` for CSR arrays that live on the GPU (index bookkeeping with torch on the sampled tiles only;
+	one scalar is read back)."""
+	torch = _torch()
+	nt = -(-n // tile)
+	if nt == 0 or colidx.numel() == 0:
+		return 0.0
+	dev = rowptr.device
+	ts = torch.unique(torch.linspace(0, nt - 1, min(nt, sample), device=dev).long())
+	r0 = ts * tile
+	r1 = torch.clamp(r0 + tile, max=n)
+	rp = rowptr.long()
+	lo, hi = rp[r0], rp[r1]
+	cnt = hi - lo
+	total = int(cnt.sum().item())
+	if total == 0:
+		return 0.0
+	start = torch.cumsum(cnt, 0) - cnt
+	idx = torch.repeat_interleave(lo - start, cnt) + torch.arange(total, device=dev)
+	c = colidx[idx].long()
+	a, b = torch.repeat_interleave(r0, cnt), torch.repeat_interleave(r1, cnt)
+	off = int(((c < a) | (c >= b)).sum().item())
+	return off / max(int((r1 - r0).sum().item()), 1)
+
+
 def _balance_tiles(weights: np.ndarray, ncta: int) -> np.ndarray:
 	"""Tile placement for a persistent grid: returns `place` with place[j] = the tile to put at position j, where
 	position j is processed by CTA j % ncta.  Longest-processing-time greedy with the per-CTA tile counts fixed (heaviest
@@ -180,6 +225,9 @@ class DeviceOperator:
 	matrix/array (any format; converted to CSR once, not per call), or any object with `.matvec` and `.shape`
 	(slow host-callback path, include/pylinop.h:17-40).  The matrix is uploaded ONCE per operator.
 
+	`fused` (sparse input): "auto" lets the one-kernel Lanczos step (DESIGN 3 "fused step") run where it pays -- at most
+	1.75 non-zeros per row outside their 120-row tile, measured on the final row order -- True / False force it.
+
 	`tiled` (dense fp64 input): keep a band-major copy of the matrix for the tensor-core product kernel ("auto": when it
 	fits comfortably; False: row-major only; results are bit-identical either way).
 
@@ -190,7 +238,7 @@ class DeviceOperator:
 	order is internal: every vector that crosses the API is in the caller's row order.
 	"""
 
-	def __init__(self, A: Any, dtype=None, reorder="auto", tiled="auto"):
+	def __init__(self, A: Any, dtype=None, reorder="auto", tiled="auto", fused="auto"):
 		import scipy.sparse as sp
 
 		torch = _torch()
@@ -206,6 +254,7 @@ class DeviceOperator:
 		self._handle = ctypes.c_void_p()
 		self.h2d_bytes = 0
 		self.tiled = False
+		self.fused_step, self.offtile_per_row = True, None  # (the library's default wherever this class does not decide)
 		dev = torch.device("cuda", torch.cuda.current_device())
 		if sp.issparse(A) and A.format in ("coo", "bsr") and not (isinstance(reorder, int) and not isinstance(reorder, bool) and reorder > 1) \
 				and reorder is not True and not _want_reorder(reorder, self.n, int(A.nnz)):
@@ -220,6 +269,12 @@ class DeviceOperator:
 			self.kind, self.nnz = "csr", int(colidx.numel())
 			_ffi.check(L.slq_csr_create_ex(self.n, self.nnz, rowptr.data_ptr(), colidx.data_ptr(), vals.data_ptr(), self.code,
 			                               int(lens.max().item()) if self.n else 0, None, ctypes.byref(self._handle)))  # fmt: skip
+			if isinstance(fused, str) and fused == "auto":
+				self.offtile_per_row = float("inf") if self.perm is not None else _offtile_per_row_device(rowptr, colidx, self.n)
+				self.fused_step = self.offtile_per_row <= FUSED_MAX_OFFTILE
+			else:
+				self.fused_step = bool(fused)
+			_ffi.check(L.slq_op_set_fused_step(self._handle, int(self.fused_step)))
 		elif sp.issparse(A):
 			if A.format == "csc":
 				# a symmetric matrix in CSC form IS its CSR form (A^T = A): no conversion, exactly the arrays the reference's
@@ -261,6 +316,11 @@ class DeviceOperator:
 			# the longest row is known on the host (a symmetric permutation keeps the row lengths): no device work, no sync
 			_ffi.check(L.slq_csr_create_ex(self.n, self.nnz, rowptr.data_ptr(), colidx.data_ptr(), vals.data_ptr(), self.code,
 			                               int(np.diff(C.indptr).max(initial=0)), None, ctypes.byref(self._handle)))  # fmt: skip
+			# one-kernel Lanczos step (orth = 0): it reads two rows per gathered non-zero, so it is kept for operators whose
+			# non-zeros mostly stay inside a row tile (ip / ix are the arrays in the operator's final row order)
+			self.offtile_per_row = _offtile_per_row(ip, ix) if not balance else float("inf")
+			self.fused_step = (self.offtile_per_row <= FUSED_MAX_OFFTILE) if (isinstance(fused, str) and fused == "auto") else bool(fused)
+			_ffi.check(L.slq_op_set_fused_step(self._handle, int(self.fused_step)))
 		elif isinstance(A, np.ndarray) or (hasattr(A, "is_cuda") and hasattr(A, "data_ptr")):
 			M = A if hasattr(A, "data_ptr") else torch.from_numpy(np.ascontiguousarray(A, dtype=self.dtype))
 			M = M.to(dev, dtype=_tdtype(self.dtype))
@@ -307,7 +367,7 @@ class DeviceOperator:
 			self.perm = None
 
 	@classmethod
-	def from_device_csr(cls, rowptr, colidx, vals, n: int, dtype=None, reorder=False):
+	def from_device_csr(cls, rowptr, colidx, vals, n: int, dtype=None, reorder=False, fused="auto"):
 		"""Operator from CSR arrays that already live on the GPU (torch tensors: int32 rowptr (n+1), int32 colidx, float
 		vals; column indices sorted per row recommended).  No host copy is made unless a locality ordering is asked for
 		(`reorder=True` or a cluster size), which runs on the host (slq_csr_cluster_order / slq_csr_permute).
@@ -324,6 +384,7 @@ class DeviceOperator:
 		vals = vals.to(_tdtype(self.dtype)).contiguous()
 		assert rowptr.is_cuda and colidx.is_cuda and vals.is_cuda and rowptr.numel() == self.n + 1
 		self.perm, self.h2d_bytes = None, 0
+		self.tiled, self.fused_step, self.offtile_per_row = False, True, None
 		if isinstance(reorder, str) and reorder == "balance":
 			rowptr, colidx, vals, self.perm = _balance_rows_device(rowptr, colidx, vals, self.n, REORDER_TILE)
 		elif reorder:
@@ -343,6 +404,13 @@ class DeviceOperator:
 		# longest row computed on the CURRENT stream (the arrays may still be in flight there) and read back: documented sync
 		_ffi.check(L.slq_csr_create_ex(self.n, self.nnz, rowptr.data_ptr(), colidx.data_ptr(), vals.data_ptr(), self.code,
 		                               -1, _stream_ptr(), ctypes.byref(self._handle)))  # fmt: skip
+		if isinstance(fused, str) and fused == "auto":
+			balanced = isinstance(reorder, str) and reorder == "balance"
+			self.offtile_per_row = float("inf") if balanced else _offtile_per_row_device(rowptr, colidx, self.n)
+			self.fused_step = self.offtile_per_row <= FUSED_MAX_OFFTILE
+		else:
+			self.fused_step = bool(fused)
+		_ffi.check(L.slq_op_set_fused_step(self._handle, int(self.fused_step)))
 		self._ws = {}
 		return self
 

@@ -18,7 +18,7 @@ def _both(A, X, deg, dtype=np.float64):
 
 	from primate_b200 import engine
 
-	op = engine.DeviceOperator(A, dtype=dtype)
+	op = engine.DeviceOperator(A, dtype=dtype, fused=True)
 	Xd = torch.from_numpy(np.ascontiguousarray(X, dtype=dtype)).cuda()
 	fused = op.lanczos(op._to_internal(Xd.clone()), deg, 1e-8, 0, 2)
 	plain = op.lanczos(op._to_internal(Xd.clone()), deg, 1e-8, 0, max(deg, 2), want_basis=True)
@@ -51,7 +51,7 @@ def test_fused_step_vs_reference_at_c2_parameters(oracle):
 	st, inc = oracle.pcg64_state(7)
 	X = engine.rademacher_block(st, inc, 0, 64, n, np.float64)
 	W = X.cpu().numpy().copy()
-	op = engine.DeviceOperator(A)
+	op = engine.DeviceOperator(A, fused=True)
 	out = op.lanczos(op._to_internal(X), 50, 1e-8, 0, 2)
 	al, be = out["alpha"].cpu().numpy(), out["beta"].cpu().numpy()
 	for p in (0, 31, 63):
@@ -93,3 +93,31 @@ def test_fused_step_mixed_breakdown_columns_and_degree_one():
 	assert abs(fa[2, 0] - ew[10]) < 1e-12 * ew[10]
 	(fa1, fb1, fs1, _), (pa1, pb1, ps1, _) = _both(A, X, 1)
 	assert np.all(fs1 == 1) and rel_err(fa1[:, 0], pa1[:, 0]) < 1e-12
+
+
+def test_fused_step_policy_and_switch():
+	"""`fused="auto"`: on for a mesh in the locality order (C2's operator: 0.74 off-tile non-zeros per row), off for a 3-D
+	7-point Laplacian (2.7 per row even after the ordering: the doubled gathers cost more than the saved panel passes);
+	`fused=False` takes the two-kernel step (same results as asking for the basis)."""
+	import torch
+
+	from primate_b200 import engine
+
+	A2 = laplacian_2d(300)  # n = 90 000 >= the reorder threshold
+	op2 = engine.DeviceOperator(A2)
+	assert op2.perm is not None and op2.offtile_per_row < 1.2 and op2.fused_step
+	T = sp.diags([-1.0, 2.0, -1.0], [-1, 0, 1], shape=(44, 44))
+	I = sp.identity(44)  # noqa: E741
+	A3 = (sp.kron(sp.kron(T, I), I) + sp.kron(sp.kron(I, T), I) + sp.kron(sp.kron(I, I), T)).tocsr()
+	op3 = engine.DeviceOperator(A3)
+	assert op3.offtile_per_row > 2.0 and not op3.fused_step
+	X = np.random.default_rng(0).standard_normal((A2.shape[0], 16))
+	Xd = torch.from_numpy(X).cuda()
+	outs = []
+	for fused in (True, False):
+		op = engine.DeviceOperator(A2, fused=fused)
+		assert op.fused_step == fused
+		o = op.lanczos(op._to_internal(Xd.clone()), 25, 1e-8, 0, 2)
+		outs.append((o["alpha"].cpu().numpy(), o["beta"].cpu().numpy()))
+	assert rel_err(outs[0][0][:, :25], outs[1][0][:, :25]) < 1e-11 and rel_err(outs[0][1][:, 1:25], outs[1][1][:, 1:25]) < 1e-11
+	assert not np.array_equal(outs[0][1][:, 25], np.zeros(16))
