@@ -410,11 +410,13 @@ def run_ours_report(args, world, ms, value, launches, clk, prof, e2e, rec, n, nn
 	tB, cB, _ = prof["axpy"]
 	avgA = tA / max(cA, 1)  # ms
 	avgB = tB / max(cB, 1)
-	fused = cA > 0 and cB == 0  # one kernel per Lanczos step (k_stepA_tma<STEP_FUSED>): no separate axpy launches were seen
+	# one kernel per Lanczos step (k_stepA_tma<STEP_FUSED>) for every block of >= 8 probes: (next to) no separate axpy launches
+	# were seen (a rank's last block of < 8 probes still takes the generic two-kernel path: 1 block of 20 at N = 8)
+	fused = cA > 0 and cB * 4 < cA
 	if fused:
 		# the fused step: CSR once + read the pending w and its vector u + write the formed vector and the new w; the first
 		# step of a block reads the start block (twice, the second time from L2) and writes only w
-		stepA_bytes = sum(deg * csr_bytes + (4 * deg - 2) * n * k * 8 for k in blocks) / (deg * len(blocks))
+		stepA_bytes = sum(deg * csr_bytes + ((4 * deg - 2) if k >= 8 else (3 * deg - 1)) * n * k * 8 for k in blocks) / (deg * len(blocks))
 		kernel = ("k_stepA_tma<STEP_FUSED>: the WHOLE Lanczos step in one kernel (CSR SpMM on the vector formed on the fly from the "
 		          "previous step's w and u, beta*q_p subtraction, alpha dot, norm sums; TMA-staged tiles) -- 4 panel passes per step "
 		          "instead of the 6 of SURVEY 8d's two-kernel step")  # fmt: skip
