@@ -76,6 +76,9 @@ __device__ __forceinline__ void cp_async_wait() {
 #ifndef SLQ_TMA_RF
 #define SLQ_TMA_RF 1
 #endif
+#ifndef SLQ_TMA_FUSED_STREAM_ST
+XX
+#endif
 #ifndef SLQ_TMA_RF512
 #define SLQ_TMA_RF512 1
 #endif
@@ -515,8 +518,8 @@ __global__ void __launch_bounds__(TmaTiling<T, K, LONGROWS, MODE == STEP_FUSED>:
                     acc_w[FUSED ? q : 0] += (double)wv.v[q] * (double)wv.v[q];
                     acc_v[FUSED ? q : 0] += (double)vn.v[q] * (double)vn.v[q];
                   }
-                  if (rp.Y) st_pack<T, V, false>(reinterpret_cast<T*>(rp.Y) + off, vn);
-                  st_pack<T, V, false>(w + off, wv);
+                  if (rp.Y) st_pack<T, V, SLQ_TMA_FUSED_STREAM_ST != 0>(reinterpret_cast<T*>(rp.Y) + off, vn);
+                  st_pack<T, V, SLQ_TMA_FUSED_STREAM_ST != 0>(w + off, wv);
                 }
               }
             }
