@@ -63,24 +63,29 @@ def _want_reorder(reorder, n: int, nnz: int) -> bool:
 FUSED_MAX_OFFTILE = 1.75  # off-tile non-zeros per row up to which the one-kernel Lanczos step pays (slq_op_set_fused_step)
 
 
-def _offtile_per_row(indptr: np.ndarray, indices: np.ndarray, tile: int = REORDER_TILE, sample: int = 2000) -> float:
+def _offtile_per_row(indptr: np.ndarray, indices: np.ndarray, tile: int = REORDER_TILE, sample: int = 512) -> float:
 	"""Non-zeros per row whose column lies outside the row's tile of `tile` consecutive rows, estimated on `sample`
-	evenly spaced tiles (host CSR arrays; a few tens of milliseconds whatever nnz is)."""
+	evenly spaced tiles (host CSR arrays; about a millisecond whatever nnz is)."""
 	n = len(indptr) - 1
 	nt = -(-n // tile)
-	if nt == 0:
+	if nt == 0 or len(indices) == 0:
 		return 0.0
-	off = rows = 0
-	for t in np.unique(np.linspace(0, nt - 1, min(nt, sample)).astype(np.int64)):
-		r0 = int(t) * tile
-		r1 = min(n, r0 + tile)
-		c = indices[indptr[r0] : indptr[r1]]
-		off += int(np.count_nonzero((c < r0) | (c >= r1)))
-		rows += r1 - r0
-	return off / max(rows, 1)
+	ts = np.unique(np.linspace(0, nt - 1, min(nt, sample)).astype(np.int64))
+	r0 = ts * tile
+	r1 = np.minimum(r0 + tile, n)
+	lo, hi = indptr[r0].astype(np.int64), indptr[r1].astype(np.int64)
+	cnt = hi - lo
+	total = int(cnt.sum())
+	if total == 0:
+		return 0.0
+	start = np.cumsum(cnt) - cnt
+	idx = np.repeat(lo - start, cnt) + np.arange(total, dtype=np.int64)
+	c = indices[idx]
+	off = int(np.count_nonzero((c < np.repeat(r0, cnt)) | (c >= np.repeat(r1, cnt))))
+	return off / max(int((r1 - r0).sum()), 1)
 
 
-def _offtile_per_row_device(rowptr, colidx, n: int, tile: int = REORDER_TILE, sample: int = 2000) -> float:
+def _offtile_per_row_device(rowptr, colidx, n: int, tile: int = REORDER_TILE, sample: int = 512) -> float:
 	"""`_offtile_per_row` for CSR arrays that live on the GPU (index bookkeeping with torch on the sampled tiles only;
 	one scalar is read back)."""
 	torch = _torch()
