@@ -1006,8 +1006,9 @@ static int lanczos_impl(slq_op* op, T* X, int deg, double rtol, int orth, int nc
           freep.pop_back();
         }
         const int pslot = prof_begin(PROF_STEPA, st);
-        int rc = launch_stepA_fused<T, K>(op, P[iW], P[iU], P[iWn], iV >= 0 ? P[iV] : nullptr, ws.sc, scale_of(j % 3), scale_of((j + 2) % 3),
-                                          scale_of((j + 1) % 3), ws.partial, so, st);
+        // (first step: beta = 0 multiplies the "previous" scale, which must be a finite number, not an unwritten row)
+        int rc = launch_stepA_fused<T, K>(op, P[iW], P[iU], P[iWn], iV >= 0 ? P[iV] : nullptr, ws.sc, scale_of(j % 3),
+                                          j > 0 ? scale_of((j + 2) % 3) : scale_of(0), scale_of((j + 1) % 3), ws.partial, so, st);
         if (rc != SLQ_OK) return rc;
         prof_end(PROF_STEPA, pslot, st);
         if (j > 0) {

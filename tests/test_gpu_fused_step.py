@@ -121,3 +121,23 @@ def test_fused_step_policy_and_switch():
 		outs.append((o["alpha"].cpu().numpy(), o["beta"].cpu().numpy()))
 	assert rel_err(outs[0][0][:, :25], outs[1][0][:, :25]) < 1e-11 and rel_err(outs[0][1][:, 1:25], outs[1][1][:, 1:25]) < 1e-11
 	assert not np.array_equal(outs[0][1][:, 25], np.zeros(16))
+
+
+@pytest.mark.parametrize("fused", [True, False])
+def test_lanczos_does_not_read_unwritten_workspace(fused):
+	"""The caller's workspace arrives with arbitrary contents: poisoned with NaN bit patterns between two identical calls,
+	the coefficients must not change (the first fused step multiplies beta_0 = 0 by the scale of a "previous" vector)."""
+	import torch
+
+	from primate_b200 import engine
+
+	A = (laplacian_2d(40) + 0.5 * sp.identity(1600)).tocsr()
+	X = torch.from_numpy(np.random.default_rng(2).standard_normal((1600, 16))).cuda()
+	op = engine.DeviceOperator(A, fused=fused)
+	a = op.lanczos(X.clone(), 12, 1e-8, 0, 2)
+	for buf in op._ws.values():
+		buf.fill_(0xFF)  # every double / float in the workspace becomes a NaN
+	b = op.lanczos(X.clone(), 12, 1e-8, 0, 2)
+	for key in ("alpha", "beta", "steps", "xnorm2"):
+		assert torch.equal(a[key], b[key]), key
+	assert torch.isfinite(b["alpha"]).all() and torch.isfinite(b["beta"]).all()
