@@ -367,7 +367,9 @@ def run_ours(args) -> None:
 		e2e = {"value": total_probe_steps / (float(ems.item()) * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
 		       "d2h_bytes_per_step": int(8 * P if world == 1 else 24), "ms_per_step": float(ems.item()) / args.steps,
 		       "wall_ms_per_step": 1e3 * wall / args.steps, "estimate": float(est),
-		       "api": "hutch(MatrixFunction(A_host_csr, 'log', deg, orth=0), converge='count', count=P, seed=rng)"}  # fmt: skip
+		       "api": "hutch(MatrixFunction(A_host_csr, 'log', deg, orth=0), converge='count', count=P, seed=rng)",
+		       "ingestion": "every step, every rank: new MatrixFunction from the pinned host CSR -> row permutation applied on the host "
+		                    "(the locality ORDER itself is remembered per sparsity structure after the warm-up step) -> H2D of the CSR -> device operator"}  # fmt: skip
 
 	if rank != 0:
 		if world > 1:

@@ -60,6 +60,36 @@ def _want_reorder(reorder, n: int, nnz: int) -> bool:
 	return bool(reorder)
 
 
+_ORDER_CACHE: dict = {}  # (n, nnz, tile, structure fingerprint) -> locality permutation (host int32 array); at most 4 entries
+
+
+def _structure_key(indptr: np.ndarray, indices: np.ndarray, tile: int) -> tuple:
+	"""Cheap fingerprint of a CSR sparsity structure: sizes + a hash of <= 64k evenly spaced entries of each index array.
+	Used ONLY to re-use a locality ordering: any permutation is a valid one (P A P^T has the spectrum of A and the
+	estimators are invariant under it), so a collision could cost locality, never correctness."""
+	import hashlib
+
+	h = hashlib.blake2b(digest_size=16)
+	for a in (indptr, indices):
+		step = max(1, len(a) // 65536)
+		h.update(np.ascontiguousarray(a[::step]).tobytes())
+	return (len(indptr) - 1, len(indices), int(tile), h.hexdigest())
+
+
+def _cluster_order(L, n: int, ip: np.ndarray, ix: np.ndarray, tile: int) -> np.ndarray:
+	"""slq_csr_cluster_order with the result remembered per sparsity structure (a MatrixFunction rebuilt on the same matrix
+	-- another f, another degree, the next step of a solver loop -- does not repeat the breadth-first clustering)."""
+	key = _structure_key(ip, ix, tile)
+	perm = _ORDER_CACHE.get(key)
+	if perm is None:
+		perm = np.empty(n, dtype=np.int32)
+		_ffi.check(L.slq_csr_cluster_order(n, ip.ctypes.data, ix.ctypes.data, tile, perm.ctypes.data))
+		if len(_ORDER_CACHE) >= 4:
+			_ORDER_CACHE.pop(next(iter(_ORDER_CACHE)))
+		_ORDER_CACHE[key] = perm
+	return perm
+
+
 FUSED_MAX_OFFTILE = 1.75  # off-tile non-zeros per row up to which the one-kernel Lanczos step pays (slq_op_set_fused_step)
 
 
@@ -301,8 +331,7 @@ class DeviceOperator:
 			if not balance and _want_reorder(reorder, self.n, int(C.nnz)):
 				# locality ordering (slq_csr_cluster_order): rows grouped into breadth-first clusters of one SpMM row tile
 				tile = int(reorder) if (isinstance(reorder, int) and not isinstance(reorder, bool) and reorder > 1) else int(os.environ.get("SLQ_REORDER_TILE", REORDER_TILE))
-				perm = np.empty(self.n, dtype=np.int32)
-				_ffi.check(L.slq_csr_cluster_order(self.n, ip.ctypes.data, ix.ctypes.data, tile, perm.ctypes.data))
+				perm = _cluster_order(L, self.n, ip, ix, tile)
 				ip2, ix2, va2 = np.empty_like(ip), np.empty_like(ix), np.empty_like(va)
 				_ffi.check(L.slq_csr_permute(self.n, ip.ctypes.data, ix.ctypes.data, va.ctypes.data, self.code, perm.ctypes.data,
 				                             ip2.ctypes.data, ix2.ctypes.data, va2.ctypes.data))  # fmt: skip
@@ -395,8 +424,7 @@ class DeviceOperator:
 		elif reorder:
 			tile = int(reorder) if (isinstance(reorder, int) and not isinstance(reorder, bool) and reorder > 1) else REORDER_TILE
 			ip, ix, va = rowptr.cpu().numpy(), colidx.cpu().numpy(), vals.cpu().numpy()
-			perm = np.empty(self.n, dtype=np.int32)
-			_ffi.check(L.slq_csr_cluster_order(self.n, ip.ctypes.data, ix.ctypes.data, tile, perm.ctypes.data))
+			perm = _cluster_order(L, self.n, ip, ix, tile)
 			ip2, ix2, va2 = np.empty_like(ip), np.empty_like(ix), np.empty_like(va)
 			_ffi.check(L.slq_csr_permute(self.n, ip.ctypes.data, ix.ctypes.data, va.ctypes.data, self.code, perm.ctypes.data,
 			                             ip2.ctypes.data, ix2.ctypes.data, va2.ctypes.data))  # fmt: skip

@@ -265,3 +265,31 @@ def test_gathered_samples_keep_genuine_nans():
 	rows = [np.array([1.0, np.nan, 3.0]), np.array([4.0, 5.0, 6.0]), np.array([7.0, 0.0, 0.0])]  # 7 probes over 3 ranks: 3 + 3 + 1
 	got = trace._gather_ranges(rows[1], 7, FakeComm(rows))
 	assert got.shape == (7,) and np.isnan(got[1]) and np.array_equal(got[[0, 2, 3, 4, 5, 6]], [1.0, 3.0, 4.0, 5.0, 6.0, 7.0])
+
+
+def test_locality_ordering_is_remembered_per_sparsity_structure():
+	"""engine._cluster_order: the second request for the same structure returns the remembered permutation without
+	calling the clustering again; another structure (or tile) is clustered afresh; every result is a permutation."""
+	import scipy.sparse as sp
+
+	from primate_b200 import _ffi, engine
+
+	from .conftest import laplacian_2d
+
+	L = _ffi.lib()
+	engine._ORDER_CACHE.clear()
+	A = laplacian_2d(40)
+	ip, ix = np.ascontiguousarray(A.indptr, dtype=np.int32), np.ascontiguousarray(A.indices, dtype=np.int32)
+	p1 = engine._cluster_order(L, A.shape[0], ip, ix, 120)
+	assert len(engine._ORDER_CACHE) == 1 and np.array_equal(np.sort(p1), np.arange(A.shape[0]))
+	p2 = engine._cluster_order(L, A.shape[0], ip.copy(), ix.copy(), 120)
+	assert p2 is p1  # same structure in other arrays: remembered
+	p3 = engine._cluster_order(L, A.shape[0], ip, ix, 60)
+	assert p3 is not p1 and len(engine._ORDER_CACHE) == 2
+	B = (A + sp.diags([1.0], [7], shape=A.shape) + sp.diags([1.0], [-7], shape=A.shape)).tocsr()
+	bp, bx = np.ascontiguousarray(B.indptr, dtype=np.int32), np.ascontiguousarray(B.indices, dtype=np.int32)
+	p4 = engine._cluster_order(L, B.shape[0], bp, bx, 120)
+	assert p4 is not p1 and np.array_equal(np.sort(p4), np.arange(B.shape[0]))
+	for i in range(5):  # bounded
+		engine._cluster_order(L, A.shape[0], ip, ix, 100 + i)
+	assert len(engine._ORDER_CACHE) <= 4
