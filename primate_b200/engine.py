@@ -140,6 +140,30 @@ def _offtile_per_row_device(rowptr, colidx, n: int, tile: int = REORDER_TILE, sa
 	return off / max(int((r1 - r0).sum().item()), 1)
 
 
+def _permute_csr_device(rowptr, colidx, vals, perm, n: int):
+	"""P A P^T for CSR arrays on the GPU (perm[new] = old), rows sorted by their new column indices: the arrays
+	slq_csr_permute produces on the host, bit for bit, without the host pass over nnz (index bookkeeping with torch:
+	one radix sort of row * n + column keys).  Returns (rowptr int32, colidx int32, vals)."""
+	import torch
+
+	dev = rowptr.device
+	rp = rowptr.long()
+	deg = rp[1:] - rp[:-1]
+	p = perm.long()
+	inv = torch.empty(n, dtype=torch.int64, device=dev)
+	inv[p] = torch.arange(n, device=dev)
+	oldrow = torch.repeat_interleave(torch.arange(n, device=dev), deg)
+	key = inv[oldrow] * n + inv[colidx.long()]
+	del oldrow
+	key, order = torch.sort(key)
+	ncol = (key % n).int()
+	del key
+	nval = vals[order]
+	nrp = torch.zeros(n + 1, dtype=torch.int64, device=dev)
+	nrp[1:] = torch.cumsum(deg[p], 0)
+	return nrp.int(), ncol, nval
+
+
 def _balance_tiles(weights: np.ndarray, ncta: int) -> np.ndarray:
 	"""Tile placement for a persistent grid: returns `place` with place[j] = the tile to put at position j, where
 	position j is processed by CTA j % ncta.  Longest-processing-time greedy with the per-CTA tile counts fixed (heaviest
@@ -331,16 +355,15 @@ class DeviceOperator:
 			if not balance and _want_reorder(reorder, self.n, int(C.nnz)):
 				# locality ordering (slq_csr_cluster_order): rows grouped into breadth-first clusters of one SpMM row tile
 				tile = int(reorder) if (isinstance(reorder, int) and not isinstance(reorder, bool) and reorder > 1) else int(os.environ.get("SLQ_REORDER_TILE", REORDER_TILE))
-				perm = _cluster_order(L, self.n, ip, ix, tile)
-				ip2, ix2, va2 = np.empty_like(ip), np.empty_like(ix), np.empty_like(va)
-				_ffi.check(L.slq_csr_permute(self.n, ip.ctypes.data, ix.ctypes.data, va.ctypes.data, self.code, perm.ctypes.data,
-				                             ip2.ctypes.data, ix2.ctypes.data, va2.ctypes.data))  # fmt: skip
-				ip, ix, va = ip2, ix2, va2
-				self.perm = torch.from_numpy(perm).to(dev)
+				# (the order comes from the host -- breadth-first clustering, remembered per structure -- but it is APPLIED on
+				# the device: the caller's arrays are uploaded as they are, no host pass over nnz)
+				self.perm = torch.from_numpy(_cluster_order(L, self.n, ip, ix, tile)).to(dev)
 			rowptr = torch.from_numpy(ip).to(dev, non_blocking=False)
 			colidx = torch.from_numpy(ix).to(dev)
 			vals = torch.from_numpy(va).to(dev)
 			self.h2d_bytes = rowptr.numel() * 4 + colidx.numel() * 4 + vals.numel() * vals.element_size()
+			if self.perm is not None:
+				rowptr, colidx, vals = _permute_csr_device(rowptr, colidx, vals, self.perm, self.n)
 			if balance:
 				rowptr, colidx, vals, self.perm = _balance_rows_device(rowptr, colidx, vals, self.n, REORDER_TILE)
 			self._keep = [rowptr, colidx, vals]
@@ -352,7 +375,7 @@ class DeviceOperator:
 			                               int(np.diff(C.indptr).max(initial=0)), None, ctypes.byref(self._handle)))  # fmt: skip
 			# one-kernel Lanczos step (orth = 0): it reads two rows per gathered non-zero, so it is kept for operators whose
 			# non-zeros mostly stay inside a row tile (ip / ix are the arrays in the operator's final row order)
-			self.offtile_per_row = _offtile_per_row(ip, ix) if not balance else float("inf")
+			self.offtile_per_row = float("inf") if balance else (_offtile_per_row(ip, ix) if self.perm is None else _offtile_per_row_device(rowptr, colidx, self.n))
 			self.fused_step = (self.offtile_per_row <= FUSED_MAX_OFFTILE) if (isinstance(fused, str) and fused == "auto") else bool(fused)
 			_ffi.check(L.slq_op_set_fused_step(self._handle, int(self.fused_step)))
 		elif isinstance(A, np.ndarray) or (hasattr(A, "is_cuda") and hasattr(A, "data_ptr")):
@@ -404,7 +427,8 @@ class DeviceOperator:
 	def from_device_csr(cls, rowptr, colidx, vals, n: int, dtype=None, reorder=False, fused="auto"):
 		"""Operator from CSR arrays that already live on the GPU (torch tensors: int32 rowptr (n+1), int32 colidx, float
 		vals; column indices sorted per row recommended).  No host copy is made unless a locality ordering is asked for
-		(`reorder=True` or a cluster size), which runs on the host (slq_csr_cluster_order / slq_csr_permute).
+		(`reorder=True` or a cluster size): the clustering runs on the host on a copy of the index arrays
+		(slq_csr_cluster_order), the permutation is applied on the device.
 		`reorder="balance"` is the ordering for power-law graphs (no locality to find, but hub rows that would pile up in a
 		few row tiles): rows are dealt to the row tiles in order of decreasing length, entirely on the device."""
 		torch = _torch()
@@ -423,14 +447,10 @@ class DeviceOperator:
 			rowptr, colidx, vals, self.perm = _balance_rows_device(rowptr, colidx, vals, self.n, REORDER_TILE)
 		elif reorder:
 			tile = int(reorder) if (isinstance(reorder, int) and not isinstance(reorder, bool) and reorder > 1) else REORDER_TILE
-			ip, ix, va = rowptr.cpu().numpy(), colidx.cpu().numpy(), vals.cpu().numpy()
-			perm = _cluster_order(L, self.n, ip, ix, tile)
-			ip2, ix2, va2 = np.empty_like(ip), np.empty_like(ix), np.empty_like(va)
-			_ffi.check(L.slq_csr_permute(self.n, ip.ctypes.data, ix.ctypes.data, va.ctypes.data, self.code, perm.ctypes.data,
-			                             ip2.ctypes.data, ix2.ctypes.data, va2.ctypes.data))  # fmt: skip
-			dev = rowptr.device
-			rowptr, colidx, vals = torch.from_numpy(ip2).to(dev), torch.from_numpy(ix2).to(dev), torch.from_numpy(va2).to(dev)
-			self.perm = torch.from_numpy(perm).to(dev)
+			# only the index structure visits the host (for the clustering); the permutation is applied on the device
+			ip, ix = rowptr.cpu().numpy(), colidx.cpu().numpy()
+			self.perm = torch.from_numpy(_cluster_order(L, self.n, ip, ix, tile)).to(rowptr.device)
+			rowptr, colidx, vals = _permute_csr_device(rowptr, colidx, vals, self.perm, self.n)
 		self._keep = [rowptr, colidx, vals]
 		self.kind, self.nnz = "csr", int(colidx.numel())
 		self._handle = ctypes.c_void_p()

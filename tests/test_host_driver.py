@@ -293,3 +293,34 @@ def test_locality_ordering_is_remembered_per_sparsity_structure():
 	for i in range(5):  # bounded
 		engine._cluster_order(L, A.shape[0], ip, ix, 100 + i)
 	assert len(engine._ORDER_CACHE) <= 4
+
+
+def test_device_side_permutation_equals_slq_csr_permute():
+	"""engine._permute_csr_device (torch index bookkeeping; CPU tensors here) produces exactly the arrays of the host
+	routine slq_csr_permute -- rows in the new order, columns relabelled and sorted -- so moving the permutation to the
+	device changed no operator bit."""
+	import scipy.sparse as sp
+	import torch
+
+	from primate_b200 import _ffi, engine
+
+	from .conftest import laplacian_2d
+
+	L = _ffi.lib()
+	rng = np.random.default_rng(0)
+	R = sp.random(2000, 2000, density=0.004, random_state=1)
+	R = (R + R.T).tolil()
+	R[5, :] = 1.0
+	R[:, 5] = 1.0  # one long row / column; some rows stay empty
+	for A, dtype, code in ((laplacian_2d(50), np.float64, _ffi.SLQ_F64), (R.tocsr(), np.float32, _ffi.SLQ_F32)):
+		C = A.tocsr().astype(dtype)
+		C.sort_indices()
+		n = C.shape[0]
+		ip, ix = np.ascontiguousarray(C.indptr, dtype=np.int32), np.ascontiguousarray(C.indices, dtype=np.int32)
+		va = np.ascontiguousarray(C.data, dtype=dtype)
+		for perm in (engine._cluster_order(L, n, ip, ix, 120), rng.permutation(n).astype(np.int32)):
+			ip2, ix2, va2 = np.empty_like(ip), np.empty_like(ix), np.empty_like(va)
+			_ffi.check(L.slq_csr_permute(n, ip.ctypes.data, ix.ctypes.data, va.ctypes.data, code, perm.ctypes.data, ip2.ctypes.data,
+			                             ix2.ctypes.data, va2.ctypes.data))  # fmt: skip
+			r, c, v = engine._permute_csr_device(torch.from_numpy(ip), torch.from_numpy(ix), torch.from_numpy(va), torch.from_numpy(perm), n)
+			assert np.array_equal(r.numpy(), ip2) and np.array_equal(c.numpy(), ix2) and np.array_equal(v.numpy(), va2)
