@@ -324,3 +324,29 @@ def test_device_side_permutation_equals_slq_csr_permute():
 			                             ix2.ctypes.data, va2.ctypes.data))  # fmt: skip
 			r, c, v = engine._permute_csr_device(torch.from_numpy(ip), torch.from_numpy(ix), torch.from_numpy(va), torch.from_numpy(perm), n)
 			assert np.array_equal(r.numpy(), ip2) and np.array_equal(c.numpy(), ix2) and np.array_equal(v.numpy(), va2)
+
+
+def test_offtile_estimate_matches_brute_force(monkeypatch):
+	"""engine._offtile_per_row (sampled tiles, host arrays) and its torch twin against a brute-force count; the numbers
+	behind the fused-step policy: a 2-D mesh in natural order ~2 off-tile non-zeros per row, ~0.75 after the ordering."""
+	import torch
+
+	from primate_b200 import _ffi, engine
+
+	from .conftest import laplacian_2d
+
+	A = laplacian_2d(150)
+	n = A.shape[0]
+	ip, ix = np.ascontiguousarray(A.indptr, dtype=np.int32), np.ascontiguousarray(A.indices, dtype=np.int32)
+	rows = np.repeat(np.arange(n), np.diff(ip))
+	brute = np.count_nonzero(rows // 120 != ix // 120) / n
+	est = engine._offtile_per_row(ip, ix, sample=10**6)  # every tile
+	assert abs(est - brute) < 1e-12
+	assert abs(engine._offtile_per_row(ip, ix) - brute) < 0.1  # the default sample
+	monkeypatch.setattr(engine, "_torch", lambda: torch)
+	dev = engine._offtile_per_row_device(torch.from_numpy(ip), torch.from_numpy(ix), n, sample=10**6)
+	assert abs(dev - brute) < 1e-12
+	perm = engine._cluster_order(_ffi.lib(), n, ip, ix, 120)
+	r, c, _ = engine._permute_csr_device(torch.from_numpy(ip), torch.from_numpy(ix), torch.from_numpy(A.data.copy()), torch.from_numpy(perm), n)
+	after = engine._offtile_per_row(r.numpy(), c.numpy())
+	assert brute > 1.5 and after < 1.0 and after <= engine.FUSED_MAX_OFFTILE < brute
